@@ -1,0 +1,225 @@
+/* pcb200.h -- C ABI of the B200-native solver core for the Pencil Code.
+ *
+ * This is the drop-in boundary: the Fortran module `GPU` (public list in the
+ * reference's src/gpu.h:1 -- gpu_init, register_GPU, initialize_GPU,
+ * finalize_GPU, rhs_GPU, copy_farray_from_GPU) is re-implemented by
+ * pencil-code_b200/fortran/gpu_b200.f90 on top of the entry points below
+ * through ISO_C_BINDING.  Every entry point names the reference interface it
+ * replaces.  Plain pointers and sizes only; all reals are FP64
+ * (REAL_PRECISION=double), all integers 32 bit (FINT, src/headers_c.h:15).
+ *
+ * Every function returns 0 on success and a negative PCB200_E* code on
+ * failure; pcb200_last_error() gives the message.  There is NO CPU fallback:
+ * without a CUDA device pcb200_init() fails.
+ */
+#ifndef PCB200_H
+#define PCB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCB200_ABI_VERSION 1
+#define PCB200_MAXVAR 8      /* ux uy uz lnrho ss ax ay az */
+#define PCB200_NGHOST 3      /* src/deriv.f90:7 / cparam.f90 nghost */
+
+/* error codes */
+#define PCB200_OK          0
+#define PCB200_ENODEV     -1  /* no CUDA device / driver            */
+#define PCB200_EUNSUPP    -2  /* unsupported module / flag combo    */
+#define PCB200_EARG       -3  /* bad argument                       */
+#define PCB200_ECUDA      -4  /* CUDA runtime error                 */
+#define PCB200_ESTATE     -5  /* call out of order                  */
+#define PCB200_ENCCL      -6  /* NCCL error                         */
+
+/* boundary-condition codes, one per variable and face.
+ * Reference strings (run.in bcx/bcy/bcz, src/boundcond.f90:1283-1460):
+ *  'p' periodic, 's' symmetric, 'a' antisymmetric, 'a2' antisym. rel. to
+ *  boundary value, 'c1' constant heat flux (ss, bottom; bc_ss_flux
+ *  eos_idealgas.f90:2245), 'cT' constant temperature (ss; bc_ss_temp_z
+ *  eos_idealgas.f90:3434). */
+enum {
+  PCB200_BC_P  = 0,
+  PCB200_BC_S  = 1,
+  PCB200_BC_A  = 2,
+  PCB200_BC_A2 = 3,
+  PCB200_BC_C1 = 4,
+  PCB200_BC_CT = 5
+};
+
+/* heat conduction choice (entropy.f90 iheatcond) */
+enum {
+  PCB200_HCOND_NONE     = 0,
+  PCB200_HCOND_KPROFILE = 1,  /* 'K-profile', calc_heatcond entropy.f90:5333      */
+  PCB200_HCOND_CHICONST = 2   /* 'chi-const', calc_heatcond_constchi :4266        */
+};
+
+/* Flat parameter block filled by the Fortran wrapper from cdata/cparam and the
+ * module run_pars (replaces the generated cparam_c.h/cdata_c.h headers and the
+ * pushpars2c pointer tables, gpu_astaroth_ansi.c:31-35, astaroth/gpu_astaroth.cc:242-317).
+ * Variable slots are 1-based Fortran indices (iux..iaz in cdata), 0 = absent. */
+typedef struct pcb200_params {
+  int32_t abi_version;            /* must be PCB200_ABI_VERSION              */
+  /* local (per rank) interior sizes and process layout (cparam.f90:18-55)  */
+  int32_t nx, ny, nz;
+  int32_t nprocx, nprocy, nprocz;
+  int32_t ipx, ipy, ipz;
+  int32_t lperi[3];               /* cdata lperi                             */
+  int32_t mvar, mfarray;
+  int32_t iux, iuy, iuz, ilnrho, iss, iax, iay, iaz;
+  /* module switches (Makefile.local choices -> cparam l* constants)        */
+  int32_t lhydro, ldensity, lentropy, lmagnetic, lgravz, lforcing;
+  int32_t lupw_uu, lupw_lnrho, lupw_ss;   /* hydro/density/entropy run_pars  */
+  int32_t lbidiagonal_derij;      /* cdata.f90:568; only 1 is supported      */
+  int32_t iheatcond;              /* PCB200_HCOND_*                          */
+  int32_t lcooling;               /* entropy cool/=0 (get_heat_cool_gravz)   */
+  int32_t lviscosity_heat;        /* entropy.f90:132                         */
+  int32_t lohmic_heat;            /* magnetic lohmic_heat                    */
+  int32_t ldt;                    /* cdata ldt: dt from CFL (1) or fixed (0) */
+  int32_t reserved_i[7];
+  /* BC codes [face 0=lower,1=upper][variable slot-1]                       */
+  int32_t bcx[2][PCB200_MAXVAR];
+  int32_t bcy[2][PCB200_MAXVAR];
+  int32_t bcz[2][PCB200_MAXVAR];
+  /* equidistant Cartesian grid of this rank (grid.f90 construct_grid)      */
+  double dx, dy, dz;              /* cdata dx,dy,dz                          */
+  double dx_1, dy_1, dz_1;        /* cdata dx_1(l1),dy_1(m1),dz_1(n1): the
+                                     host's own 1/dx (grid.f90:218), not 1/dx
+                                     recomputed                              */
+  double dz2_bound[7];            /* grid.f90:2670-2672, index i+3, i=-3..3  */
+  double xyz0[3];                 /* lower corner of the GLOBAL box          */
+  double Lxyz[3];
+  double x0_loc, y0_loc, z0_loc;  /* x(l1), y(m1), z(n1) of this rank        */
+  /* time step control (cdata.f90:145-153)                                  */
+  double cdt, cdtv, cdts, dtmax, dt_fixed;
+  double alpha_ts[3], beta_ts[3]; /* timestep.f90:40-41                      */
+  /* physics                                                                */
+  double nu;                      /* viscosity_run_pars, ivisc='nu-const'    */
+  double eta;                     /* magnetic_run_pars, iresistivity='eta-const' */
+  double mu0;                     /* cdata.f90:252                           */
+  double cs20, gamma, cp, lnrho0; /* eos (units_eos eos_idealgas.f90:123)    */
+  double Omega;                   /* hydro_run_pars, theta=0                 */
+  double gravz;                   /* gravity_simple gravz_profile='const'    */
+  double chi;                     /* entropy chi (chi-const)                 */
+  double hcond0, hcond1, hcond2;  /* entropy K-profile, lmultilayer          */
+  double z1, z2, widthss;         /* gravity z1,z2 ; entropy widthss         */
+  double cool, wcool, cs2cool;    /* entropy cooling layer                   */
+  double ztop;                    /* xyz0(3)+Lxyz(3)                         */
+  double Fbot;                    /* entropy Fbot (bc 'c1')                  */
+  double cs2top;                  /* entropy cs2top (bc 'cT')                */
+  double reserved_d[8];
+} pcb200_params;
+
+/* helical forcing coefficients for one time step; the random wave vector and
+ * phase stay on the host (forcing.f90:1554-1849 fconst_coefs_hel/fxyz_coefs_hel;
+ * consumed like forcing_pars_hel, astaroth/forcing.h:19).
+ * f_u_j += Re[(coef1_j + i coef2_j) * fx(l) fy(m) fz(n)] * fda_j  (forcing.f90:1968-2110) */
+typedef struct pcb200_forcing {
+  double coef1[3], coef2[3], fda[3];
+  double kk[3];                   /* wave vector * k1_ff                     */
+  double phase;                   /* random phase                            */
+  double fact;                    /* force/ffnorm*sqrt(dt)  (forcing.f90:1741) */
+} pcb200_forcing;
+
+/* indices into the diagnostics vector returned by pcb200_get_diagnostics
+ * (replaces calc_0d_diagnostics_* accumulation via sum_mn_name/max_mn_name,
+ * diagnostics.f90:1686-1886; raw sums/maxima of this rank -- the caller
+ * finishes them exactly like diagnostic(), diagnostics.f90:643-716). */
+enum {
+  PCB200_DIAG_U2SUM = 0,  /* sum u^2            -> urms = sqrt(sum/nw)       */
+  PCB200_DIAG_U2MAX,      /* max u^2            -> umax = sqrt(max)          */
+  PCB200_DIAG_RHOSUM,     /* sum rho            -> rhom                      */
+  PCB200_DIAG_SSSUM,      /* sum ss             -> ssm                       */
+  PCB200_DIAG_B2SUM,      /* sum b^2            -> brms                      */
+  PCB200_DIAG_B2MAX,      /* max b^2            -> bmax                      */
+  PCB200_DIAG_J2SUM,      /* sum j^2            -> jrms                      */
+  PCB200_DIAG_J2MAX,      /* max j^2            -> jmax                      */
+  PCB200_DIAG_DTC,        /* max sqrt(advec_cs2)/cdt      (x dt -> dtc)      */
+  PCB200_DIAG_DTU,        /* max advec_uu/cdt             (x dt -> dtu)      */
+  PCB200_DIAG_DTNU,       /* max nu*dxyz_2/cdtv           (x dt -> dtnu)     */
+  PCB200_DIAG_DTCHI,      /* max diffus_chi/cdtv          (x dt -> dtchi)    */
+  PCB200_DIAG_DT1MAX,     /* max dt1 of this rank (1/dt before allreduce)    */
+  PCB200_DIAG_ABSUM,      /* sum a.b            -> abm                       */
+  PCB200_DIAG_JBSUM,      /* sum j.b            -> jbm                       */
+  PCB200_DIAG_OUSUM,      /* sum o.u            -> oum                       */
+  PCB200_NDIAG = 16
+};
+
+/* gpu_init (run.f90:125; init_gpu_c_ gpu_astaroth_ansi.c:46): pick the
+ * device for this rank (local_rank) and create streams. */
+int pcb200_init(int local_rank);
+
+/* initialize_GPU (register.f90:375; initialize_gpu_c_ :37): upload
+ * parameters, (re)allocate device buffers. Idempotent (RELOAD, run.f90:571). */
+int pcb200_initialize(const pcb200_params *par);
+
+/* register_GPU (run.f90:223; register_gpu_c_ :54): remember the address of
+ * the host array f(mx,my,mz,mfarray) (aliased, never freed). */
+int pcb200_register(double *f_host);
+
+/* rhs_GPU (equ.f90:343; rhs_gpu_c_ :89): one RK substep (BCs, halo exchange,
+ * RHS, CFL dt on substep 1, 2N-RK3 update) fully on the device.
+ * isubstep in {1,2,3}; full!=0 uploads the registered host f first
+ * (lvery_first, gpu_astaroth.f90:107,124); early_finalize is accepted for
+ * interface parity (the device always completes halos itself).
+ * ldiagnos!=0 also accumulates the 0-D diagnostics on substep 1.
+ * *dt (in/out): on substep 1 with ldt the new time step is returned. */
+int pcb200_substep(int isubstep, int full, int early_finalize, int ldiagnos, double *dt);
+
+/* One full time step = 3 x pcb200_substep + optional forcing kick, for
+ * callers that do not need per-substep control (bench, tests). */
+int pcb200_timestep(int full, int ldiagnos, double *dt);
+
+/* copy_farray_from_GPU (equ.f90:345, snapshot.f90:286; copy_farray_c_ :130):
+ * download all mvar variables incl. ghosts into f_host (NULL = the registered
+ * array). */
+int pcb200_copy_farray(double *f_host);
+
+/* upload f from the host (NULL = registered array) -- `full` path stand-alone */
+int pcb200_load_farray(const double *f_host);
+
+/* addforce/forcing_hel (run.f90:729; forcing.f90:1851): coefficients for the
+ * kick applied after substep 3 of the current step.  Pass NULL to disable. */
+int pcb200_set_forcing(const pcb200_forcing *frc);
+
+/* 1-D z profiles the entropy module precomputes on the host (nz values for
+ * n=n1..n2 of this rank): hcond_prof/dlnhcond_prof (get_gravz_heatcond,
+ * entropy.f90:7243-7262, used by get_prof_pencil :7379) and the cooling
+ * profile prof(z) of get_heat_cool_gravz (entropy.f90:6244-6272). */
+enum { PCB200_PROF_HCOND = 0, PCB200_PROF_DLNHCOND = 1, PCB200_PROF_COOL = 2, PCB200_NPROF = 3 };
+int pcb200_set_zprofile(int which, const double *prof, int nz);
+
+/* 0-D diagnostics of the last substep-1 call made with ldiagnos!=0.  */
+int pcb200_get_diagnostics(double *out, int n);
+
+/* Multi-GPU: NCCL communicator bootstrap.  Rank 0 calls get_unique_id and
+ * the host broadcasts the 128 bytes (MPI_Bcast in the Fortran wrapper,
+ * torch.distributed in bench.py); then every rank calls comm_init.
+ * Replaces mpicomm_init's Cartesian setup (mpicomm.f90:367-605). */
+int pcb200_nccl_unique_id(char id128[128]);
+int pcb200_comm_init(const char id128[128], int rank, int nranks);
+
+/* finalize_GPU (register.f90:455; finalize_gpu_c_ :62) */
+int pcb200_finalize(void);
+
+/* timing helpers on the library's own compute stream (bench.py; the host
+ * prints 'Wall clock time/timestep/meshpoint', run.f90:939-941) */
+int pcb200_timer_start(void);
+int pcb200_timer_stop(float *ms);
+int pcb200_sync(void);
+/* number of kernels launched by the library since the last call (resets) */
+int64_t pcb200_launch_count(void);
+/* average duration [ms] and count of the fused RHS+RK kernel launches since
+ * the last call (CUDA events on the compute stream; resets) */
+int pcb200_rhs_kernel_time(float *avg_ms, int *count);
+int pcb200_enable_kernel_timing(int on);
+
+const char *pcb200_last_error(void);
+int pcb200_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCB200_H */

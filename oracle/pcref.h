@@ -1,0 +1,67 @@
+/* pcref.h -- CPU ORACLE (test infrastructure, NOT product code).
+ *
+ * A restatement in C of the Pencil Code's pencil-wise RHS / 2N-RK3 hot path
+ * (reference: /root/reference/src/{deriv,sub,hydro,density,noentropy,entropy,
+ * eos_idealgas,viscosity,magnetic,gravity_simple,boundcond,equ,timestep}.f90).
+ * Each function cites the file:line it follows and keeps the Fortran order of
+ * floating-point operations (compile with -ffp-contract=off).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load this library.  The product (libpcb200.so)
+ * never links or calls it.
+ *
+ * PARITY PIN: the reference is Fortran+MPI and cannot be compiled in this
+ * image (no Fortran compiler).  The oracle is pinned against the reference's
+ * own golden time series samples/conv-slab/reference.out.double through
+ * tests/test_oracle_convslab.py (initial condition restated in
+ * oracle/initcond.py); see DESIGN.md "Oracle".
+ */
+#ifndef PCREF_H
+#define PCREF_H
+#include "../include/pcb200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* deriv.f90 stencils on one point; f points at the variable's (mx,my,mz) block,
+ * (l,m,n) are 0-based indices including ghosts; j = 1,2,3 axis. */
+double pcref_der (const double *f, int mx, int my, int l, int m, int n, int j, double d_1);
+double pcref_der2(const double *f, int mx, int my, int l, int m, int n, int j, double d_1);
+double pcref_der6_upwind(const double *f, int mx, int my, int l, int m, int n, int j, double d_1);
+double pcref_derij(const double *f, int mx, int my, int l, int m, int n, int i, int j,
+                   double di_1, double dj_1);
+
+/* whole-array versions used by the unit tests (interior only, out has nx*ny*nz) */
+void pcref_der_field (const double *f, int nx, int ny, int nz, int j, double d_1, double *out);
+void pcref_der2_field(const double *f, int nx, int ny, int nz, int j, double d_1, double *out);
+void pcref_der6_field(const double *f, int nx, int ny, int nz, int j, double d_1, double *out);
+void pcref_derij_field(const double *f, int nx, int ny, int nz, int i, int j,
+                       double di_1, double dj_1, double *out);
+
+/* boundconds_x/y/z on the full ghost-padded array (boundcond.f90:659,1018,1283),
+ * single domain (the oracle always runs the global grid on one process). */
+void pcref_boundconds(double *f, const pcb200_params *par);
+
+/* rhs_cpu mn-loop (equ.f90:816-1239): df += RHS(f).  If lfirst, *dt1_max is
+ * updated (must be initialised by the caller, equ.f90:280-290); if diag!=NULL
+ * (PCB200_NDIAG doubles, zero-initialised by the caller) the 0-D diagnostics
+ * are accumulated. */
+void pcref_rhs(const double *f, double *df, const pcb200_params *par,
+               int lfirst, double *dt1_max, double *diag);
+
+/* time_step (timestep.f90:65-198): 3 substeps incl. boundary conditions,
+ * set_dt (sub.f90:3896) and the optional forcing kick (run.f90:729).
+ * df is scratch (mx*my*mz*mvar). *dt in/out. */
+void pcref_timestep(double *f, double *df, const pcb200_params *par,
+                    const pcb200_forcing *frc, double *dt, double *diag);
+
+/* forcing_hel application (forcing.f90:1968-2110) */
+void pcref_addforce(double *f, const pcb200_params *par, const pcb200_forcing *frc);
+
+int pcref_num_threads(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

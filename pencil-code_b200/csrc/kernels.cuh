@@ -1,0 +1,469 @@
+// kernels.cuh -- CUDA kernels of the solver core (sm_100a).
+//
+//  rhs_march<MAG,ENT,AUXM>   fused RHS + 2N-RK3 update, z-marching: each CTA
+//      owns a 32x8 (x,y) tile and marches along z; ghost-padded z-planes are
+//      staged in a shared-memory ring with cp.async (8 slots: 7 live + 1 in
+//      flight), the thread's own z-column lives in a register sliding window.
+//  rhs_global<MAG,ENT,AUXM>  same physics straight from global memory (L1/L2
+//      cached); used for thin boundary slabs and as an in-library cross-check.
+//  bc_*                      ghost-zone fills (boundcond.f90 semantics).
+//  axpy_update               f_out = f_in + c*w   (substep 1 when dt comes from
+//      the CFL reduction of the same substep, timestep.f90:148-163).
+//  reduce_partials           deterministic second pass of the dt/diagnostic
+//      reductions (no floating-point atomics).
+#pragma once
+#include "physics.cuh"
+#include <cuda_runtime.h>
+
+__constant__ DevPar c_par;
+
+// reduction slots
+enum { RD_DT1 = 0, RD_U2MAX, RD_B2MAX, RD_J2MAX, RD_DTC, RD_DTU, RD_DTNU, RD_DTCHI, NRMAX,
+       RS_U2 = NRMAX, RS_RHO, RS_SS, RS_B2, RS_J2, RS_AB, RS_JB, RS_OU, NRED };
+
+#define TX 32
+#define TY 8
+#define NTHR (TX * TY)
+#define HX (TX + 2 * NG)
+#define HY (TY + 2 * NG)
+#define PE (HX * HY)          // elements of one staged plane tile
+#define NSLOT 8
+
+struct SubstepArgs {
+  const double *f_in;
+  double *w;
+  double *f_out;
+  double alpha;       // w = alpha*w + rhs   (alpha==0: w is not read)
+  double beta;        // f_out = f_in + beta*dt*w  (timestep.f90:152,162)
+  const double *dt_dev;   // dt lives on the device: no host round trip inside a step
+  int write_w;        // 0 on the last substep
+  int write_f;        // 0 on substep 1 when dt is not yet known
+  double *partials;   // [nblocks][NRED] when AUXM>0
+  int z_lo, z_hi;     // range of output planes (interior-relative, [z_lo,z_hi))
+  int zchunk;
+};
+
+// ------------------------------------------------------------------------
+// warp/block reduction of the auxiliary quantities (deterministic order)
+// red[NRED] per thread; first NRMAX are maxima, the rest sums.
+// AUXM==1: only RD_DT1 is reduced.
+// ------------------------------------------------------------------------
+template <int AUXM>
+__device__ __forceinline__ void block_reduce_store(const double *red, int tid, int nthreads,
+                                                   double *sm, double *partials, int block_linear)
+{
+  const int nq = AUXM == 1 ? 1 : NRED;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int nwarp = (nthreads + 31) >> 5;
+#pragma unroll
+  for (int q = 0; q < NRED; q++) {
+    if (q >= nq) break;
+    double v = red[q];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double t = __shfl_xor_sync(0xffffffffu, v, o);
+      v = q < NRMAX ? fmax(v, t) : v + t;
+    }
+    if (lane == 0) sm[warp * NRED + q] = v;
+  }
+  __syncthreads();
+  if (tid < nq) {
+    double v = sm[tid];
+    for (int wv = 1; wv < nwarp; wv++) v = tid < NRMAX ? fmax(v, sm[wv * NRED + tid]) : v + sm[wv * NRED + tid];
+    partials[(size_t)block_linear * NRED + tid] = v;
+  }
+}
+
+__global__ void reduce_partials(const double *__restrict__ partials, int nblocks, double *__restrict__ out)
+{
+  // one block of NRED*32 threads: warp q reduces slot q in a fixed order
+  const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (q >= NRED) return;
+  double v = 0.0;
+  for (int b = lane; b < nblocks; b += 32) {
+    const double t = partials[(size_t)b * NRED + q];
+    v = q < NRMAX ? fmax(v, t) : v + t;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = q < NRMAX ? fmax(v, t) : v + t;
+  }
+  if (lane == 0) out[q] = v;
+}
+
+// ------------------------------------------------------------------------
+// accessor over global memory
+// ------------------------------------------------------------------------
+struct GlobalAcc {
+  const double *p[NROLE];
+  long long sy, sz;
+  template <int R> PC_DEV double c() const { return __ldg(p[R]); }
+  template <int R, int K> PC_DEV double x() const { return __ldg(p[R] + K); }
+  template <int R, int K> PC_DEV double y() const { return __ldg(p[R] + K * sy); }
+  template <int R, int K> PC_DEV double z() const { return __ldg(p[R] + K * sz); }
+  template <int R, int KX, int KY> PC_DEV double xy() const { return __ldg(p[R] + KX + KY * sy); }
+  template <int R, int KX, int KZ> PC_DEV double xz() const { return __ldg(p[R] + KX + KZ * sz); }
+  template <int R, int KY, int KZ> PC_DEV double yz() const { return __ldg(p[R] + KY * sy + KZ * sz); }
+};
+
+template <bool MAG, bool ENT>
+__device__ __forceinline__ void store_cell(const SubstepArgs &a, long long idx, const double *rhs)
+{
+  const DevPar &c = c_par;
+#pragma unroll
+  for (int r = 0; r < NROLE; r++) {
+    if (!MAG && (r == R_AX || r == R_AY || r == R_AZ)) continue;
+    if (!ENT && r == R_SS) continue;
+    const long long i = idx + (long long)c.slot[r] * c.mw;
+    double wv = rhs[r];
+    if (a.alpha != 0.0) wv += a.alpha * a.w[i];
+    if (a.write_w) a.w[i] = wv;
+    if (a.write_f) a.f_out[i] = a.f_in[i] + (a.beta * a.dt_dev[0]) * wv;
+  }
+}
+
+template <bool MAG, bool ENT, int AUXM>
+__global__ void __launch_bounds__(256) rhs_global(SubstepArgs a)
+{
+  const DevPar &c = c_par;
+  __shared__ double sm[8 * NRED];
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y * blockDim.y + threadIdx.y;
+  const int n = a.z_lo + blockIdx.z * blockDim.z + threadIdx.z;
+  double red[NRED];
+#pragma unroll
+  for (int q = 0; q < NRED; q++) red[q] = 0.0;
+  if (l < c.nx && m < c.ny && n < a.z_hi) {
+    const long long idx = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+    GlobalAcc acc;
+    acc.sy = c.sy; acc.sz = c.sz;
+#pragma unroll
+    for (int r = 0; r < NROLE; r++) acc.p[r] = c.slot[r] >= 0 ? a.f_in + (long long)c.slot[r] * c.mw + idx : a.f_in;
+    double rhs[NROLE];
+    CellAux aux;
+    rhs_cell<MAG, ENT, (AUXM > 0)>(acc, c, n, rhs, aux);
+    store_cell<MAG, ENT>(a, idx, rhs);
+    if (AUXM > 0) {
+      red[RD_DT1] = aux.dt1;
+      if (AUXM > 1) {
+        red[RD_U2MAX] = aux.u2; red[RD_B2MAX] = aux.b2; red[RD_J2MAX] = aux.j2;
+        red[RD_DTC] = aux.dtc; red[RD_DTU] = aux.dtu; red[RD_DTNU] = aux.dtnu; red[RD_DTCHI] = aux.dtchi;
+        red[RS_U2] = aux.u2; red[RS_RHO] = aux.rho; red[RS_SS] = aux.ss; red[RS_B2] = aux.b2; red[RS_J2] = aux.j2;
+        red[RS_AB] = aux.ab; red[RS_JB] = aux.jb; red[RS_OU] = aux.ou;
+      }
+    }
+  }
+  if (AUXM > 0) {
+    const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+    const int bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    block_reduce_store<AUXM>(red, tid, blockDim.x * blockDim.y * blockDim.z, sm, a.partials, bl);
+  }
+}
+
+// ------------------------------------------------------------------------
+// z-marching kernel with a shared-memory plane ring
+// ------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc)
+{
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+
+// Roles R_UX..R_AZ (0..5) are "ring" fields: they need x/y neighbours on the
+// planes z+-k (bidiagonal xz/yz mixed derivatives), so 7 planes are live.
+// R_LNRHO,R_SS are "plain" fields: only the centre plane is staged (2 slots).
+template <bool MAG, bool ENT>
+struct MarchAcc {
+  const double *ring;   // [ring role][NSLOT][PE]
+  const double *plain;  // [plain role][2][PE]
+  int so[7];            // element offset of the slot holding plane z+k, k=-3..3
+  int po;               // element offset of the plain-field slot of plane z
+  int tb;               // (ty+NG)*HX + tx+NG
+  double w[NROLE][7];   // own column, planes z-3..z+3
+  template <int R> PC_DEV const double *cen() const
+  { return R < 6 ? ring + (R * NSLOT) * PE + so[3] + tb : plain + ((R - 6) * 2) * PE + po + tb; }
+  template <int R> PC_DEV double c() const { return w[R][3]; }
+  template <int R, int K> PC_DEV double x() const { return cen<R>()[K]; }
+  template <int R, int K> PC_DEV double y() const { return cen<R>()[K * HX]; }
+  template <int R, int K> PC_DEV double z() const { return w[R][3 + K]; }
+  template <int R, int KX, int KY> PC_DEV double xy() const { return cen<R>()[KX + KY * HX]; }
+  template <int R, int KX, int KZ> PC_DEV double xz() const { return ring[(R * NSLOT) * PE + so[3 + KZ] + tb + KX]; }
+  template <int R, int KY, int KZ> PC_DEV double yz() const { return ring[(R * NSLOT) * PE + so[3 + KZ] + tb + KY * HX]; }
+};
+
+template <bool MAG, bool ENT> struct MarchCfg {
+  static constexpr int NRF = MAG ? 6 : 3;
+  static constexpr int NPF = ENT ? 2 : 1;
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)NRF * NSLOT * PE + (size_t)NPF * 2 * PE + 8 * NRED);
+};
+
+template <bool MAG, bool ENT> __device__ __forceinline__ bool role_present(int r)
+{
+  if (r >= R_AX && r <= R_AZ) return MAG;
+  if (r == R_SS) return ENT;
+  return true;
+}
+
+template <bool MAG, bool ENT, int AUXM>
+__global__ void __launch_bounds__(NTHR, 1) rhs_march(SubstepArgs a)
+{
+  const DevPar &c = c_par;
+  extern __shared__ double smem[];
+  double *ring = smem;
+  double *plain = smem + (size_t)MarchCfg<MAG, ENT>::NRF * NSLOT * PE;
+  double *redsm = plain + (size_t)MarchCfg<MAG, ENT>::NPF * 2 * PE;
+
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx;
+  const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;           // tile origin (interior coords == padded coords of the halo origin)
+  const int zb = a.z_lo + blockIdx.z * a.zchunk;
+  const int ze = min(zb + a.zchunk, a.z_hi);
+  const bool active = (x0 + tx < c.nx) && (y0 + ty < c.ny);
+
+  // per-thread share of a plane tile: up to 3 elements
+  int eoff[3]; long long goff[3]; bool eok[3];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int e = tid + i * NTHR;
+    const int hy = e / HX, hx = e - hy * HX;
+    eoff[i] = e;
+    eok[i] = e < PE && (x0 + hx) < c.mx && (y0 + hy) < c.my;
+    goff[i] = (long long)(y0 + hy) * c.sy + (x0 + hx);
+  }
+  // column offset of this thread in a plane
+  const long long col = (long long)(y0 + ty + NG) * c.sy + (x0 + tx + NG);
+
+  MarchAcc<MAG, ENT> acc;
+  acc.ring = ring; acc.plain = plain;
+  acc.tb = (ty + NG) * HX + tx + NG;
+
+  // prologue: ring planes zb-3..zb+3 (padded zb..zb+6) into slots 0..6, plain plane zb into slot 0
+#pragma unroll 1
+  for (int q = 0; q < 7; q++) {
+    const long long pz = (long long)(zb + q) * c.sz;
+#pragma unroll
+    for (int r = 0; r < 6; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+      const double *src = a.f_in + (long long)c.slot[r] * c.mw + pz;
+#pragma unroll
+      for (int i = 0; i < 3; i++) if (eok[i]) cp_async8(ring + ((size_t)r * NSLOT + q) * PE + eoff[i], src + goff[i]);
+    }
+  }
+#pragma unroll
+  for (int r = 6; r < NROLE; r++) {
+    if (!role_present<MAG, ENT>(r)) continue;
+    const double *src = a.f_in + (long long)c.slot[r] * c.mw + (long long)(zb + NG) * c.sz;
+#pragma unroll
+    for (int i = 0; i < 3; i++) if (eok[i]) cp_async8(plain + ((size_t)(r - 6) * 2) * PE + eoff[i], src + goff[i]);
+  }
+  cp_async_commit();
+  // register window: planes zb-3..zb+3 of the own column
+  double wnext[NROLE];
+#pragma unroll
+  for (int r = 0; r < NROLE; r++) {
+    if (!role_present<MAG, ENT>(r)) continue;
+    const double *src = a.f_in + (long long)c.slot[r] * c.mw + col;
+#pragma unroll
+    for (int k = 0; k < 7; k++) acc.w[r][k] = active ? __ldg(src + (long long)(zb + k) * c.sz) : 0.0;
+  }
+  double red[NRED];
+#pragma unroll
+  for (int q = 0; q < NRED; q++) red[q] = 0.0;
+  const double beta_dt = a.write_f ? a.beta * a.dt_dev[0] : 0.0;
+  cp_async_wait_all();
+  __syncthreads();
+
+#pragma unroll 1
+  for (int n = zb; n < ze; n++) {
+    const int q0 = n - zb;                       // ring plane index of z-3
+    // 1. stage the next planes (ring: plane q0+7 == padded n+7 ; plain: padded n+NG+1)
+    if (n + 1 < ze) {
+      const int sl = (q0 + 7) & (NSLOT - 1);
+      const long long pz = (long long)(n + 7) * c.sz;
+#pragma unroll
+      for (int r = 0; r < 6; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        const double *src = a.f_in + (long long)c.slot[r] * c.mw + pz;
+#pragma unroll
+        for (int i = 0; i < 3; i++) if (eok[i]) cp_async8(ring + ((size_t)r * NSLOT + sl) * PE + eoff[i], src + goff[i]);
+      }
+      const int ps = (q0 + 1) & 1;
+      const long long pz1 = (long long)(n + NG + 1) * c.sz;
+#pragma unroll
+      for (int r = 6; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        const double *src = a.f_in + (long long)c.slot[r] * c.mw + pz1;
+#pragma unroll
+        for (int i = 0; i < 3; i++) if (eok[i]) cp_async8(plain + ((size_t)(r - 6) * 2 + ps) * PE + eoff[i], src + goff[i]);
+      }
+      cp_async_commit();
+#pragma unroll
+      for (int r = 0; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        wnext[r] = active ? __ldg(a.f_in + (long long)c.slot[r] * c.mw + col + pz) : 0.0;
+      }
+    }
+    // 2. compute the cell of plane n
+#pragma unroll
+    for (int k = 0; k < 7; k++) acc.so[k] = ((q0 + k) & (NSLOT - 1)) * PE;
+    acc.po = (q0 & 1) * PE;
+    if (active) {
+      double rhs[NROLE];
+      CellAux aux;
+      rhs_cell<MAG, ENT, (AUXM > 0)>(acc, c, n, rhs, aux);
+      const long long idx = (long long)(n + NG) * c.sz + col;
+      // 3. 2N-RK3 update (timestep.f90:119-122,162-163); f_in(cell) is the window centre
+#pragma unroll
+      for (int r = 0; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        const long long i = idx + (long long)c.slot[r] * c.mw;
+        double wv = rhs[r];
+        if (a.alpha != 0.0) wv += a.alpha * a.w[i];
+        if (a.write_w) a.w[i] = wv;
+        if (a.write_f) a.f_out[i] = acc.w[r][3] + beta_dt * wv;
+      }
+      if (AUXM > 0) {
+        red[RD_DT1] = fmax(red[RD_DT1], aux.dt1);
+        if (AUXM > 1) {
+          red[RD_U2MAX] = fmax(red[RD_U2MAX], aux.u2); red[RD_B2MAX] = fmax(red[RD_B2MAX], aux.b2);
+          red[RD_J2MAX] = fmax(red[RD_J2MAX], aux.j2);
+          red[RD_DTC] = fmax(red[RD_DTC], aux.dtc); red[RD_DTU] = fmax(red[RD_DTU], aux.dtu);
+          red[RD_DTNU] = fmax(red[RD_DTNU], aux.dtnu); red[RD_DTCHI] = fmax(red[RD_DTCHI], aux.dtchi);
+          red[RS_U2] += aux.u2; red[RS_RHO] += aux.rho; red[RS_SS] += aux.ss; red[RS_B2] += aux.b2; red[RS_J2] += aux.j2;
+          red[RS_AB] += aux.ab; red[RS_JB] += aux.jb; red[RS_OU] += aux.ou;
+        }
+      }
+    }
+    // 4. retire the oldest plane, admit the new one
+    cp_async_wait_all();
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+#pragma unroll
+      for (int k = 0; k < 6; k++) acc.w[r][k] = acc.w[r][k + 1];
+      acc.w[r][6] = wnext[r];
+    }
+  }
+  if (AUXM > 0) {
+    const int bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    block_reduce_store<AUXM>(red, tid, NTHR, redsm, a.partials, bl);
+  }
+}
+
+// ------------------------------------------------------------------------
+// streaming update for substep 1 when dt comes out of the same substep:
+// f_out = f_in + c*w on the interior (timestep.f90:162-163)
+// ------------------------------------------------------------------------
+__global__ void axpy_update(const double *__restrict__ f_in, const double *__restrict__ w, double *__restrict__ f_out,
+                            const double *__restrict__ dt_dev, double beta)
+{
+  const DevPar &c = c_par;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y;
+  const int nv = blockIdx.z;               // n + nz*var
+  const int n = nv % c.nz, k = nv / c.nz;
+  if (l >= c.nx) return;
+  const long long i = (long long)k * c.mw + (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+  f_out[i] = f_in[i] + (beta * dt_dev[0]) * w[i];
+}
+
+// dt = 1/max(dt1, 1/dtmax) (equ.f90:280-290, sub.f90:3911) from the reduced partials
+__global__ void finish_dt(const double *__restrict__ red, double dt1_floor, double *__restrict__ dt_dev)
+{
+  if (threadIdx.x == 0) { const double d = fmax(red[RD_DT1], dt1_floor); dt_dev[1] = d; dt_dev[0] = 1.0 / d; }
+}
+__global__ void set_dt_from_dt1(double *__restrict__ dt_dev)   // after the cross-rank max of dt_dev[1]
+{
+  if (threadIdx.x == 0) dt_dev[0] = 1.0 / dt_dev[1];
+}
+
+// ------------------------------------------------------------------------
+// helical forcing kick (forcing.f90:1968-2110 with default switches)
+// ------------------------------------------------------------------------
+struct ForcingArgs { double coef1[3], coef2[3], fda[3], kk[3], phase, fact, x0, y0, z0, dx, dy, dz; };
+__global__ void forcing_kick(double *__restrict__ f, ForcingArgs g)
+{
+  const DevPar &c = c_par;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y, n = blockIdx.z;
+  if (l >= c.nx) return;
+  double sx, cx, sy, cy, sz, cz;
+  sincos(g.kk[0] * (g.x0 + l * g.dx) + g.phase, &sx, &cx);
+  sincos(g.kk[1] * (g.y0 + m * g.dy), &sy, &cy);
+  sincos(g.kk[2] * (g.z0 + n * g.dz), &sz, &cz);
+  const double fxr = cx * g.fact, fxi = sx * g.fact;
+  const double pr = fxr * cy - fxi * sy, pi = fxr * sy + fxi * cy;
+  const double qr = pr * cz - pi * sz, qi = pr * sz + pi * cz;
+  const long long idx = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const long long i = idx + (long long)c.slot[R_UX + j] * c.mw;
+    f[i] += g.fda[j] * (g.coef1[j] * qr - g.coef2[j] * qi);
+  }
+}
+
+// ------------------------------------------------------------------------
+// boundary conditions: one thread per ghost line, all variables and both
+// faces in the reference order (bot: var 1..mvar, top: var 1..mvar;
+// boundcond.f90:1303-1316).  axis 0/1/2 = x/y/z; lines span the FULL extent
+// of the two other axes.  do_face[f]==0 skips a face (interior process
+// boundary: ghosts come from the neighbour rank instead).
+// ------------------------------------------------------------------------
+struct BcArgs {
+  double *f;
+  int axis;
+  int do_face[2];
+  int code[2][PCB200_MAXVAR];
+  int ilnrho, iss;             // storage slots
+  double cp, cv, cv1, gamma_m1, cs20, lnrho0, cs2top, Fbot, FbotKbot, chi;
+  int chiconst;
+  double dz2_bound[7];
+};
+__global__ void bc_fill(BcArgs b)
+{
+  const DevPar &c = c_par;
+  const int mm[3] = {c.mx, c.my, c.mz};
+  const int nn[3] = {c.nx, c.ny, c.nz};
+  const long long str[3] = {1, c.sy, c.sz};
+  const int ax = b.axis, bx = ax == 0 ? 1 : 0, cx = ax == 2 ? 1 : 2;   // b = fastest remaining axis
+  const int ib = blockIdx.x * blockDim.x + threadIdx.x, ic = blockIdx.y;
+  if (ib >= mm[bx] || ic >= mm[cx]) return;
+  const long long sa = str[ax];
+  const int n1 = NG, n2 = NG + nn[ax] - 1;
+  const long long line = ib * str[bx] + ic * str[cx];
+  for (int face = 0; face < 2; face++) {
+    if (!b.do_face[face]) continue;
+    for (int k = 0; k < c.mvar; k++) {
+      double *p = b.f + (long long)k * c.mw + line;
+      const int code = b.code[face][k];
+      if (code == PCB200_BC_P) {
+        if (face == 0) { for (int i = 0; i < NG; i++) p[i * sa] = p[(n2 - NG + 1 + i) * sa]; }
+        else           { for (int i = 0; i < NG; i++) p[(n2 + 1 + i) * sa] = p[(n1 + i) * sa]; }
+      } else if (code == PCB200_BC_S || code == PCB200_BC_A) {
+        const double sgn = code == PCB200_BC_S ? 1.0 : -1.0;
+        if (face == 0) { for (int i = 1; i <= NG; i++) p[(n1 - i) * sa] = sgn * p[(n1 + i) * sa]; if (sgn < 0) p[n1 * sa] = 0.0; }
+        else           { for (int i = 1; i <= NG; i++) p[(n2 + i) * sa] = sgn * p[(n2 - i) * sa]; if (sgn < 0) p[n2 * sa] = 0.0; }
+      } else if (code == PCB200_BC_A2) {
+        if (face == 0) { for (int i = 1; i <= NG; i++) p[(n1 - i) * sa] = 2.0 * p[n1 * sa] - p[(n1 + i) * sa]; }
+        else           { for (int i = 1; i <= NG; i++) p[(n2 + i) * sa] = p[n2 * sa] + (p[n2 * sa] - p[(n2 - i) * sa]); }
+      } else if (code == PCB200_BC_C1 && ax == 2 && face == 0) {
+        const double *lnr = b.f + (long long)b.ilnrho * c.mw + line;
+        const double rho_xy = exp(lnr[n1 * sa]);
+        const double cs2_xy = b.cs20 * exp(b.gamma_m1 * (lnr[n1 * sa] - b.lnrho0) + b.cv1 * p[n1 * sa]);
+        const double tmp_xy = b.chiconst ? b.Fbot / (rho_xy * b.chi * cs2_xy) : b.FbotKbot / cs2_xy;
+        for (int i = 1; i <= NG; i++) {
+          const double dlnrho = lnr[(n1 + i) * sa] - lnr[(n1 - i) * sa];
+          p[(n1 - i) * sa] = p[(n1 + i) * sa] + b.cp * (b.cp - b.cv) * (dlnrho + b.dz2_bound[3 - i] * tmp_xy);
+        }
+      } else if (code == PCB200_BC_CT && ax == 2 && face == 1) {
+        const double *lnr = b.f + (long long)b.ilnrho * c.mw + line;
+        const double tmp = 2.0 * b.cv * log(b.cs2top / b.cs20);
+        p[n2 * sa] = 0.5 * tmp - (b.cp - b.cv) * (lnr[n2 * sa] - b.lnrho0);
+        for (int i = 1; i <= NG; i++)
+          p[(n2 + i) * sa] = -p[(n2 - i) * sa] + tmp - (b.cp - b.cv) * (lnr[(n2 - i) * sa] + lnr[(n2 + i) * sa] - 2.0 * b.lnrho0);
+      }
+    }
+  }
+}

@@ -1,0 +1,522 @@
+// pcb200.cu -- C ABI (include/pcb200.h) on top of the kernels in kernels.cuh.
+//
+// Host-side orchestration of one RK substep mirrors pde()/time_step
+// (equ.f90:24-668, timestep.f90:65-198) but keeps f resident on the device:
+//   BC_x -> BC_y -> [z halo exchange over NCCL | BC_z] -> fused RHS+RK kernel
+//   -> (substep 1 with ldt) max-reduction -> dt -> streaming update.
+// No CPU fallback: every entry point fails loudly without a CUDA device.
+#include "kernels.cuh"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <dlfcn.h>
+#include <string>
+#include <vector>
+
+// ---- minimal NCCL declarations (resolved with dlopen so that single-GPU use
+// ---- does not need libnccl; same ABI as nccl.h 2.x) -----------------------
+extern "C" {
+typedef struct ncclComm *ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef int ncclResult_t;
+typedef int ncclDataType_t;   // ncclFloat64 = 8
+typedef int ncclRedOp_t;      // ncclSum=0, ncclMax=2
+}
+struct NcclApi {
+  void *h = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+struct Ctx {
+  bool inited = false, have_par = false;
+  int dev = 0;
+  cudaStream_t st = nullptr, st_comm = nullptr;
+  cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_k0 = nullptr, ev_k1 = nullptr, ev_bc = nullptr, ev_halo = nullptr, ev_inner = nullptr;
+  pcb200_params P;
+  DevPar hp;
+  size_t nelem = 0;             // mw*mvar
+  double *f[2] = {nullptr, nullptr}, *w = nullptr;
+  int cur = 0;
+  double *partials = nullptr; size_t npartials = 0;
+  double *red_dev = nullptr;    // [NRED]
+  double *dt_dev = nullptr;     // [0]=dt [1]=dt1
+  double *pinned = nullptr;     // [NRED+2]
+  double *zprof[PCB200_NPROF] = {nullptr, nullptr, nullptr};
+  double *f_host = nullptr;
+  bool have_forcing = false; pcb200_forcing frc;
+  double dt = 0.0;
+  double diag[PCB200_NDIAG];
+  bool use_global = false;      // PCB200_KERNEL=global
+  int zchunk = 0;
+  int64_t launches = 0;
+  float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
+  // multi-GPU
+  NcclApi nccl; ncclComm_t comm = nullptr; int rank = 0, nranks = 1;
+  std::string err;
+};
+static Ctx g;
+
+static int fail(int code, const std::string &msg) { g.err = msg; return code; }
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+  return fail(PCB200_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+#define NK(call) do { ncclResult_t r_ = (call); if (r_ != 0) \
+  return fail(PCB200_ENCCL, std::string(#call) + ": " + (g.nccl.GetErrorString ? g.nccl.GetErrorString(r_) : "nccl error")); } while (0)
+
+extern "C" const char *pcb200_last_error(void) { return g.err.c_str(); }
+extern "C" int pcb200_abi_version(void) { return PCB200_ABI_VERSION; }
+
+extern "C" int pcb200_init(int local_rank)
+{
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(PCB200_ENODEV, std::string("pcb200_init: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU fallback");
+  g.dev = local_rank % ndev;
+  CK(cudaSetDevice(g.dev));
+  if (!g.inited) {
+    CK(cudaStreamCreateWithFlags(&g.st, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&g.st_comm, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&g.ev_t0)); CK(cudaEventCreate(&g.ev_t1));
+    CK(cudaEventCreate(&g.ev_k0)); CK(cudaEventCreate(&g.ev_k1));
+    CK(cudaEventCreateWithFlags(&g.ev_bc, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&g.ev_halo, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&g.ev_inner, cudaEventDisableTiming));
+    CK(cudaMalloc(&g.red_dev, sizeof(double) * NRED));
+    CK(cudaMalloc(&g.dt_dev, sizeof(double) * 2));
+    CK(cudaMallocHost(&g.pinned, sizeof(double) * (NRED + 2)));
+    const char *k = getenv("PCB200_KERNEL");
+    g.use_global = k && !strcmp(k, "global");
+    const char *t = getenv("PCB200_TIME_RHS");
+    g.time_rhs = t && atoi(t) != 0;
+    g.inited = true;
+  }
+  return PCB200_OK;
+}
+
+static void free_fields()
+{
+  for (int i = 0; i < 2; i++) { if (g.f[i]) cudaFree(g.f[i]); g.f[i] = nullptr; }
+  if (g.w) cudaFree(g.w); g.w = nullptr;
+  if (g.partials) cudaFree(g.partials); g.partials = nullptr;
+}
+
+extern "C" int pcb200_initialize(const pcb200_params *par)
+{
+  if (!g.inited) return fail(PCB200_ESTATE, "pcb200_initialize before pcb200_init");
+  if (!par) return fail(PCB200_EARG, "null params");
+  if (par->abi_version != PCB200_ABI_VERSION) return fail(PCB200_EARG, "ABI version mismatch");
+  const pcb200_params &P = *par;
+  // same policy as gpu_astaroth.f90:32-71: refuse what is not implemented
+  if (!P.lhydro || !P.ldensity) return fail(PCB200_EUNSUPP, "No GPU implementation without hydro+density");
+  if (!P.lbidiagonal_derij) return fail(PCB200_EUNSUPP, "No GPU implementation for lbidiagonal_derij=F");
+  if (P.nx < 2 * NG || P.ny < 2 * NG || P.nz < 2 * NG) return fail(PCB200_EUNSUPP, "local grid smaller than 6 points per direction");
+  if (P.mvar < 4 || P.mvar > PCB200_MAXVAR) return fail(PCB200_EARG, "mvar out of range");
+  if (P.lentropy && !P.iss) return fail(PCB200_EARG, "lentropy without iss");
+  if (P.lmagnetic && !P.iax) return fail(PCB200_EARG, "lmagnetic without iax");
+  if (P.nprocx != 1 || P.nprocy != 1) return fail(PCB200_EUNSUPP, "only z-slab decomposition (nprocx=nprocy=1) is implemented");
+  if (P.nprocz != g.nranks) return fail(PCB200_EARG, "nprocz differs from the communicator size (call pcb200_comm_init first)");
+  CK(cudaSetDevice(g.dev));
+  const bool realloc = !g.have_par || g.P.nx != P.nx || g.P.ny != P.ny || g.P.nz != P.nz || g.P.mvar != P.mvar;
+  g.P = P;
+  DevPar &h = g.hp;
+  memset(&h, 0, sizeof(h));
+  h.nx = P.nx; h.ny = P.ny; h.nz = P.nz; h.mx = P.nx + 2 * NG; h.my = P.ny + 2 * NG; h.mz = P.nz + 2 * NG;
+  h.sy = h.mx; h.sz = (long long)h.mx * h.my; h.mw = h.sz * h.mz; h.mvar = P.mvar;
+  for (int r = 0; r < NROLE; r++) h.slot[r] = -1;
+  h.slot[R_UX] = P.iux - 1; h.slot[R_UY] = P.iuy - 1; h.slot[R_UZ] = P.iuz - 1; h.slot[R_LNRHO] = P.ilnrho - 1;
+  if (P.lentropy) h.slot[R_SS] = P.iss - 1;
+  if (P.lmagnetic) { h.slot[R_AX] = P.iax - 1; h.slot[R_AY] = P.iay - 1; h.slot[R_AZ] = P.iaz - 1; }
+  for (int r = 0; r < NROLE; r++) if (h.slot[r] >= P.mvar) return fail(PCB200_EARG, "variable slot beyond mvar");
+  h.lupw_uu = P.lupw_uu; h.lupw_lnrho = P.lupw_lnrho; h.lupw_ss = P.lupw_ss;
+  h.iheatcond = P.iheatcond; h.lcooling = P.lcooling; h.lviscosity_heat = P.lviscosity_heat; h.lohmic_heat = P.lohmic_heat;
+  h.lgravz = P.lgravz; h.ldensity = P.ldensity; h.lhydro = P.lhydro;
+  h.dx_1 = P.dx_1; h.dy_1 = P.dy_1; h.dz_1 = P.dz_1;
+  h.dxyz_2 = h.dx_1 * h.dx_1 + h.dy_1 * h.dy_1 + h.dz_1 * h.dz_1;
+  h.cdt = P.cdt; h.cdtv = P.cdtv; h.cdts = P.cdts;
+  h.nu = P.nu; h.eta = P.eta; h.mu0 = P.mu0; h.mu01 = 1.0 / P.mu0;
+  h.cs20 = P.cs20; h.gamma = P.gamma; h.gamma1 = 1.0 / P.gamma; h.gamma_m1 = P.gamma - 1.0;
+  h.cp = P.cp; h.cp1 = 1.0 / P.cp; h.cv = h.gamma1 * P.cp; h.cv1 = P.gamma * h.cp1; h.lnrho0 = P.lnrho0;
+  h.lnTT0 = h.gamma_m1 != 0.0 ? log(P.cs20 / (P.cp * h.gamma_m1)) : log(P.cs20 / P.cp);   // eos_idealgas.f90:230
+  h.Omega2 = 2.0 * P.Omega; h.gravz = P.gravz; h.chi = P.chi; h.cool = P.cool; h.cs2cool = P.cs2cool;
+  h.fx1 = h.dx_1 / 60.0; h.fy1 = h.dy_1 / 60.0; h.fz1 = h.dz_1 / 60.0;
+  h.fx2 = h.dx_1 * h.dx_1; h.fy2 = h.dy_1 * h.dy_1; h.fz2 = h.dz_1 * h.dz_1;
+  h.fxy = h.dx_1 * h.dy_1 / 720.0; h.fyz = h.dy_1 * h.dz_1 / 720.0; h.fzx = h.dz_1 * h.dx_1 / 720.0;
+  g.nelem = (size_t)h.mw * P.mvar;
+  if (realloc) {
+    free_fields();
+    for (int i = 0; i < 2; i++) { CK(cudaMalloc(&g.f[i], g.nelem * sizeof(double))); CK(cudaMemsetAsync(g.f[i], 0, g.nelem * sizeof(double), g.st)); }
+    CK(cudaMalloc(&g.w, g.nelem * sizeof(double)));
+    CK(cudaMemsetAsync(g.w, 0, g.nelem * sizeof(double), g.st));
+    for (int q = 0; q < PCB200_NPROF; q++) {
+      if (g.zprof[q]) cudaFree(g.zprof[q]);
+      CK(cudaMalloc(&g.zprof[q], sizeof(double) * P.nz));
+      CK(cudaMemsetAsync(g.zprof[q], 0, sizeof(double) * P.nz, g.st));
+    }
+    g.cur = 0;
+  }
+  for (int q = 0; q < PCB200_NPROF; q++) h.zprof[q] = g.zprof[q];
+  // z chunking: enough CTAs to fill 148 SMs a few times over, chunks >= 32 planes
+  {
+    const int tiles = ((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY);
+    int zc = P.nz;
+    while (zc > 32 && tiles * ((P.nz + zc - 1) / zc) < 148 * 4) zc = (zc + 1) / 2;
+    const char *e = getenv("PCB200_ZCHUNK");
+    if (e && atoi(e) > 0) zc = atoi(e);
+    g.zchunk = zc;
+  }
+  {
+    const size_t nb_m = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + g.zchunk - 1) / g.zchunk + 2);
+    const size_t nb_g = (size_t)((P.nx + 31) / 32) * ((P.ny + 3) / 4) * ((P.nz + 1) / 2 + 2);
+    const size_t need = (nb_m > nb_g ? nb_m : nb_g) * NRED;
+    if (need > g.npartials) { if (g.partials) cudaFree(g.partials); CK(cudaMalloc(&g.partials, need * sizeof(double))); g.npartials = need; }
+  }
+  CK(cudaMemcpyToSymbolAsync(c_par, &h, sizeof(DevPar), 0, cudaMemcpyHostToDevice, g.st));
+  // opt in to the large dynamic shared memory of the marching kernels
+#define OPTIN(M, E, A) CK(cudaFuncSetAttribute(rhs_march<M, E, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MarchCfg<M, E>::SMEM))
+  OPTIN(false, false, 0); OPTIN(false, false, 1); OPTIN(false, false, 2);
+  OPTIN(true, false, 0);  OPTIN(true, false, 1);  OPTIN(true, false, 2);
+  OPTIN(false, true, 0);  OPTIN(false, true, 1);  OPTIN(false, true, 2);
+  OPTIN(true, true, 0);   OPTIN(true, true, 1);   OPTIN(true, true, 2);
+#undef OPTIN
+  CK(cudaStreamSynchronize(g.st));
+  g.have_par = true;
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_set_zprofile(int which, const double *prof, int nz)
+{
+  if (!g.have_par) return fail(PCB200_ESTATE, "pcb200_set_zprofile before pcb200_initialize");
+  if (which < 0 || which >= PCB200_NPROF || !prof || nz != g.P.nz) return fail(PCB200_EARG, "bad z profile");
+  CK(cudaMemcpyAsync(g.zprof[which], prof, sizeof(double) * nz, cudaMemcpyHostToDevice, g.st));
+  CK(cudaStreamSynchronize(g.st));
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_register(double *f_host)
+{
+  if (!f_host) return fail(PCB200_EARG, "null f");
+  g.f_host = f_host;      // aliased only (astaroth/gpu_astaroth.cc:224-234)
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_load_farray(const double *f_host)
+{
+  if (!g.have_par) return fail(PCB200_ESTATE, "pcb200_load_farray before pcb200_initialize");
+  const double *src = f_host ? f_host : g.f_host;
+  if (!src) return fail(PCB200_ESTATE, "no host array registered");
+  CK(cudaMemcpyAsync(g.f[g.cur], src, g.nelem * sizeof(double), cudaMemcpyHostToDevice, g.st));
+  CK(cudaStreamSynchronize(g.st));
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_set_forcing(const pcb200_forcing *frc)
+{
+  g.have_forcing = frc != nullptr;
+  if (frc) g.frc = *frc;
+  return PCB200_OK;
+}
+
+// ------------------------------------------------------------------------
+// kernel-time bookkeeping: event pairs around every fused RHS launch,
+// resolved lazily in pcb200_rhs_kernel_time (no sync in the hot loop)
+// ------------------------------------------------------------------------
+static std::vector<cudaEvent_t> g_evpool;
+static size_t g_evused = 0;
+static bool g_time_on = false;
+extern "C" int pcb200_enable_kernel_timing(int on) { g_time_on = on != 0; g_evused = 0; return PCB200_OK; }
+static cudaEvent_t next_event()
+{
+  if (g_evused == g_evpool.size()) { cudaEvent_t e; cudaEventCreate(&e); g_evpool.push_back(e); }
+  return g_evpool[g_evused++];
+}
+extern "C" int pcb200_rhs_kernel_time(float *avg_ms, int *count)
+{
+  CK(cudaStreamSynchronize(g.st));
+  float tot = 0.f; int n = 0;
+  for (size_t i = 0; i + 1 < g_evused; i += 2) { float ms = 0.f; CK(cudaEventElapsedTime(&ms, g_evpool[i], g_evpool[i + 1])); tot += ms; n++; }
+  g_evused = 0;
+  if (avg_ms) *avg_ms = n ? tot / n : 0.f;
+  if (count) *count = n;
+  return PCB200_OK;
+}
+
+// ------------------------------------------------------------------------
+static int launch_bc(double *f, int axis, int do_lo, int do_hi)
+{
+  const pcb200_params &P = g.P; const DevPar &h = g.hp;
+  BcArgs b; memset(&b, 0, sizeof(b));
+  b.f = f; b.axis = axis; b.do_face[0] = do_lo; b.do_face[1] = do_hi;
+  const int32_t (*src)[PCB200_MAXVAR] = axis == 0 ? P.bcx : (axis == 1 ? P.bcy : P.bcz);
+  for (int fc = 0; fc < 2; fc++) for (int k = 0; k < PCB200_MAXVAR; k++) b.code[fc][k] = src[fc][k];
+  b.ilnrho = P.ilnrho - 1; b.iss = P.iss - 1;
+  b.cp = h.cp; b.cv = h.cv; b.cv1 = h.cv1; b.gamma_m1 = h.gamma_m1; b.cs20 = h.cs20; b.lnrho0 = h.lnrho0;
+  b.cs2top = P.cs2top; b.Fbot = P.Fbot; b.chi = P.chi;
+  b.FbotKbot = (P.hcond0 * P.hcond1 != 0.0) ? P.Fbot / (P.hcond0 * P.hcond1) : 0.0;    // entropy.f90:721-725
+  b.chiconst = P.iheatcond == PCB200_HCOND_CHICONST;
+  for (int i = 0; i < 7; i++) b.dz2_bound[i] = P.dz2_bound[i];
+  const int mm[3] = {h.mx, h.my, h.mz};
+  const int nb = axis == 0 ? mm[1] : mm[0], nc = axis == 2 ? mm[1] : mm[2];
+  dim3 blk(128), grd((nb + 127) / 128, nc);
+  bc_fill<<<grd, blk, 0, g.st>>>(b);
+  g.launches++;
+  CK(cudaGetLastError());
+  return PCB200_OK;
+}
+
+// z halo exchange between slabs (initiate/finalize_isendrcv_bdry, mpicomm.f90:1325-2047,
+// restricted to the z direction; x,y ghosts ride along because whole mx*my planes move)
+static int exchange_z(double *f)
+{
+  const pcb200_params &P = g.P; const DevPar &h = g.hp;
+  const int lo = g.rank - 1, hi = g.rank + 1;
+  const bool per = P.lperi[2] != 0;
+  const int nlo = lo >= 0 ? lo : (per ? g.nranks - 1 : -1);
+  const int nhi = hi < g.nranks ? hi : (per ? 0 : -1);
+  const size_t cnt = (size_t)NG * h.sz;
+  NK(g.nccl.GroupStart());
+  for (int k = 0; k < P.mvar; k++) {
+    double *b = f + (size_t)k * h.mw;
+    if (nlo >= 0) NK(g.nccl.Send(b + (size_t)NG * h.sz, cnt, 8, nlo, g.comm, g.st_comm));            // my lowest interior planes
+    if (nhi >= 0) NK(g.nccl.Recv(b + (size_t)(NG + P.nz) * h.sz, cnt, 8, nhi, g.comm, g.st_comm));   // upper ghosts
+    if (nhi >= 0) NK(g.nccl.Send(b + (size_t)P.nz * h.sz, cnt, 8, nhi, g.comm, g.st_comm));          // my highest interior planes
+    if (nlo >= 0) NK(g.nccl.Recv(b, cnt, 8, nlo, g.comm, g.st_comm));                                // lower ghosts
+  }
+  NK(g.nccl.GroupEnd());
+  return PCB200_OK;
+}
+
+template <int AUXM>
+static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_off, int *nblocks_out)
+{
+  const pcb200_params &P = g.P;
+  SubstepArgs a = a0;
+  a.z_lo = z_lo; a.z_hi = z_hi;
+  a.partials = g.partials + part_off * NRED;
+  const bool M = P.lmagnetic != 0, E = P.lentropy != 0;
+  if (z_hi <= z_lo) { *nblocks_out = 0; return PCB200_OK; }
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_time_on) { e0 = next_event(); e1 = next_event(); cudaEventRecord(e0, g.st); }
+  if (g.use_global) {
+    dim3 blk(32, 4, 2), grd((P.nx + 31) / 32, (P.ny + 3) / 4, (z_hi - z_lo + 1) / 2);
+    *nblocks_out = grd.x * grd.y * grd.z;
+    if (M && E) rhs_global<true, true, AUXM><<<grd, blk, 0, g.st>>>(a);
+    else if (M) rhs_global<true, false, AUXM><<<grd, blk, 0, g.st>>>(a);
+    else if (E) rhs_global<false, true, AUXM><<<grd, blk, 0, g.st>>>(a);
+    else rhs_global<false, false, AUXM><<<grd, blk, 0, g.st>>>(a);
+  } else {
+    a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
+    dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
+    *nblocks_out = grd.x * grd.y * grd.z;
+    if (M && E) rhs_march<true, true, AUXM><<<grd, blk, MarchCfg<true, true>::SMEM, g.st>>>(a);
+    else if (M) rhs_march<true, false, AUXM><<<grd, blk, MarchCfg<true, false>::SMEM, g.st>>>(a);
+    else if (E) rhs_march<false, true, AUXM><<<grd, blk, MarchCfg<false, true>::SMEM, g.st>>>(a);
+    else rhs_march<false, false, AUXM><<<grd, blk, MarchCfg<false, false>::SMEM, g.st>>>(a);
+  }
+  if (g_time_on) cudaEventRecord(e1, g.st);
+  g.launches++;
+  CK(cudaGetLastError());
+  return PCB200_OK;
+}
+static int launch_rhs(int auxm, const SubstepArgs &a, int z_lo, int z_hi, size_t part_off, int *nb)
+{
+  if (auxm == 0) return launch_rhs_t<0>(a, z_lo, z_hi, part_off, nb);
+  if (auxm == 1) return launch_rhs_t<1>(a, z_lo, z_hi, part_off, nb);
+  return launch_rhs_t<2>(a, z_lo, z_hi, part_off, nb);
+}
+
+static int do_substep(int isub, int ldiagnos)
+{
+  const pcb200_params &P = g.P;
+  double *fin = g.f[g.cur], *fout = g.f[1 - g.cur];
+  int rc;
+  // boundary conditions in the reference order x -> y -> z (equ.f90:211-229, boundcond.f90:1283-1290)
+  if ((rc = launch_bc(fin, 0, 1, 1))) return rc;
+  if ((rc = launch_bc(fin, 1, 1, 1))) return rc;
+  const bool multi = g.nranks > 1;
+  const bool per_z = P.lperi[2] != 0;
+  if (!multi) { if ((rc = launch_bc(fin, 2, 1, 1))) return rc; }
+  else {
+    CK(cudaEventRecord(g.ev_bc, g.st));
+    CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0));
+    if ((rc = exchange_z(fin))) return rc;
+    CK(cudaEventRecord(g.ev_halo, g.st_comm));
+    if (!per_z) {      // physical boundaries on the first/last slab only (lfirst_proc_z/llast_proc_z)
+      const int lo = g.rank == 0, hi = g.rank == g.nranks - 1;
+      if (lo || hi) if ((rc = launch_bc(fin, 2, lo, hi))) return rc;
+    }
+  }
+  const bool first = isub == 1;
+  const bool need_dt = first && P.ldt;
+  const int auxm = first ? (ldiagnos ? 2 : (need_dt ? 1 : 0)) : 0;
+  SubstepArgs a; memset(&a, 0, sizeof(a));
+  a.f_in = fin; a.w = g.w; a.f_out = fout;
+  a.alpha = first ? 0.0 : P.alpha_ts[isub - 1];
+  a.beta = P.beta_ts[isub - 1];
+  a.dt_dev = g.dt_dev;
+  a.write_w = isub < 3;
+  a.write_f = need_dt ? 0 : 1;
+  if (need_dt) a.write_w = 1;
+  int nb0 = 0, nb1 = 0, nb2 = 0;
+  if (!multi) {
+    if ((rc = launch_rhs(auxm, a, 0, P.nz, 0, &nb0))) return rc;
+  } else {
+    // interior planes overlap with the halo exchange (general.f90:267-279 / gpu_astaroth.cc:162-166)
+    if ((rc = launch_rhs(auxm, a, NG, P.nz - NG, 0, &nb0))) return rc;
+    CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0));
+    if ((rc = launch_rhs(auxm, a, 0, NG, nb0, &nb1))) return rc;
+    if ((rc = launch_rhs(auxm, a, P.nz - NG, P.nz, (size_t)nb0 + nb1, &nb2))) return rc;
+  }
+  if (auxm > 0) {
+    reduce_partials<<<1, NRED * 32, 0, g.st>>>(g.partials, nb0 + nb1 + nb2, g.red_dev);
+    g.launches++;
+    CK(cudaGetLastError());
+  }
+  if (need_dt) {
+    const double floor1 = P.dtmax != 0.0 ? 1.0 / P.dtmax : 0.0;
+    finish_dt<<<1, 32, 0, g.st>>>(g.red_dev, floor1, g.dt_dev);
+    g.launches++;
+    if (multi) {
+      NK(g.nccl.AllReduce(g.dt_dev + 1, g.dt_dev + 1, 1, 8, 2 /*ncclMax*/, g.comm, g.st));     // set_dt, sub.f90:3909
+      set_dt_from_dt1<<<1, 32, 0, g.st>>>(g.dt_dev);
+      g.launches++;
+    }
+    dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz * P.mvar);
+    axpy_update<<<grd, blk, 0, g.st>>>(fin, g.w, fout, g.dt_dev, P.beta_ts[0]);
+    g.launches++;
+    CK(cudaGetLastError());
+  }
+  g.cur ^= 1;
+  if (isub == 3 && g.have_forcing) {
+    ForcingArgs fa;
+    for (int j = 0; j < 3; j++) { fa.coef1[j] = g.frc.coef1[j]; fa.coef2[j] = g.frc.coef2[j]; fa.fda[j] = g.frc.fda[j]; fa.kk[j] = g.frc.kk[j]; }
+    fa.phase = g.frc.phase; fa.fact = g.frc.fact;
+    fa.x0 = P.x0_loc; fa.y0 = P.y0_loc; fa.z0 = P.z0_loc; fa.dx = P.dx; fa.dy = P.dy; fa.dz = P.dz;
+    dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
+    forcing_kick<<<grd, blk, 0, g.st>>>(g.f[g.cur], fa);
+    g.launches++;
+    CK(cudaGetLastError());
+  }
+  if (first && (need_dt || ldiagnos)) {
+    // dt (and the diagnostics) go back to the host: one small D2H + sync per time step
+    CK(cudaMemcpyAsync(g.pinned, g.dt_dev, sizeof(double) * 2, cudaMemcpyDeviceToHost, g.st));
+    if (auxm > 0) CK(cudaMemcpyAsync(g.pinned + 2, g.red_dev, sizeof(double) * NRED, cudaMemcpyDeviceToHost, g.st));
+    CK(cudaStreamSynchronize(g.st));
+    if (need_dt) g.dt = g.pinned[0];
+    if (ldiagnos) {
+      const double *r = g.pinned + 2;
+      double *d = g.diag;
+      d[PCB200_DIAG_U2SUM] = r[RS_U2]; d[PCB200_DIAG_U2MAX] = r[RD_U2MAX]; d[PCB200_DIAG_RHOSUM] = r[RS_RHO];
+      d[PCB200_DIAG_SSSUM] = r[RS_SS]; d[PCB200_DIAG_B2SUM] = r[RS_B2]; d[PCB200_DIAG_B2MAX] = r[RD_B2MAX];
+      d[PCB200_DIAG_J2SUM] = r[RS_J2]; d[PCB200_DIAG_J2MAX] = r[RD_J2MAX]; d[PCB200_DIAG_DTC] = r[RD_DTC];
+      d[PCB200_DIAG_DTU] = r[RD_DTU]; d[PCB200_DIAG_DTNU] = r[RD_DTNU]; d[PCB200_DIAG_DTCHI] = r[RD_DTCHI];
+      d[PCB200_DIAG_DT1MAX] = need_dt ? fmax(r[RD_DT1], P.dtmax != 0.0 ? 1.0 / P.dtmax : 0.0) : r[RD_DT1];
+      d[PCB200_DIAG_ABSUM] = r[RS_AB]; d[PCB200_DIAG_JBSUM] = r[RS_JB]; d[PCB200_DIAG_OUSUM] = r[RS_OU];
+    }
+  }
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_substep(int isubstep, int full, int early_finalize, int ldiagnos, double *dt)
+{
+  (void)early_finalize;
+  if (!g.have_par) return fail(PCB200_ESTATE, "pcb200_substep before pcb200_initialize");
+  if (isubstep < 1 || isubstep > 3) return fail(PCB200_EARG, "isubstep must be 1..3");
+  CK(cudaSetDevice(g.dev));
+  int rc;
+  if (full) { if ((rc = pcb200_load_farray(nullptr))) return rc; }
+  if (isubstep == 1 && !g.P.ldt) {
+    // fixed time step: the caller's dt (or dt_fixed) is authoritative
+    g.dt = (dt && *dt > 0.0) ? *dt : g.P.dt_fixed;
+    g.pinned[0] = g.dt; g.pinned[1] = 1.0 / g.dt;
+    CK(cudaMemcpyAsync(g.dt_dev, g.pinned, sizeof(double) * 2, cudaMemcpyHostToDevice, g.st));
+    CK(cudaStreamSynchronize(g.st));
+  }
+  if ((rc = do_substep(isubstep, ldiagnos))) return rc;
+  if (dt) *dt = g.dt;
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_timestep(int full, int ldiagnos, double *dt)
+{
+  int rc;
+  for (int s = 1; s <= 3; s++) if ((rc = pcb200_substep(s, s == 1 ? full : 0, 0, s == 1 ? ldiagnos : 0, dt))) return rc;
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_copy_farray(double *f_host)
+{
+  if (!g.have_par) return fail(PCB200_ESTATE, "pcb200_copy_farray before pcb200_initialize");
+  double *dst = f_host ? f_host : g.f_host;
+  if (!dst) return fail(PCB200_ESTATE, "no host array registered");
+  CK(cudaSetDevice(g.dev));
+  CK(cudaMemcpyAsync(dst, g.f[g.cur], g.nelem * sizeof(double), cudaMemcpyDeviceToHost, g.st));
+  CK(cudaStreamSynchronize(g.st));
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_get_diagnostics(double *out, int n)
+{
+  if (!out || n < 1) return fail(PCB200_EARG, "bad diagnostics buffer");
+  for (int i = 0; i < n && i < PCB200_NDIAG; i++) out[i] = g.diag[i];
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_nccl_unique_id(char id128[128])
+{
+  if (!g.nccl.h) {
+    const char *names[] = {"libnccl.so.2", "libnccl.so", nullptr};
+    for (int i = 0; names[i] && !g.nccl.h; i++) g.nccl.h = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+    if (!g.nccl.h) return fail(PCB200_ENCCL, std::string("cannot dlopen libnccl: ") + dlerror());
+#define SYM(n) *(void **)(&g.nccl.n) = dlsym(g.nccl.h, "nccl" #n); if (!g.nccl.n) return fail(PCB200_ENCCL, "missing symbol nccl" #n)
+    SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(Send); SYM(Recv); SYM(AllReduce); SYM(GroupStart); SYM(GroupEnd); SYM(GetErrorString);
+#undef SYM
+  }
+  if (id128) { ncclUniqueId id; NK(g.nccl.GetUniqueId(&id)); memcpy(id128, id.internal, 128); }
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_comm_init(const char id128[128], int rank, int nranks)
+{
+  if (!g.inited) return fail(PCB200_ESTATE, "pcb200_comm_init before pcb200_init");
+  if (nranks < 1 || rank < 0 || rank >= nranks) return fail(PCB200_EARG, "bad rank/nranks");
+  g.rank = rank; g.nranks = nranks;
+  if (nranks == 1) return PCB200_OK;
+  int rc = pcb200_nccl_unique_id(nullptr);
+  if (rc) return rc;
+  CK(cudaSetDevice(g.dev));
+  ncclUniqueId id; memcpy(id.internal, id128, 128);
+  NK(g.nccl.CommInitRank(&g.comm, nranks, id, rank));
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_finalize(void)
+{
+  if (!g.inited) return PCB200_OK;
+  cudaSetDevice(g.dev);
+  cudaStreamSynchronize(g.st);
+  free_fields();
+  for (int q = 0; q < PCB200_NPROF; q++) { if (g.zprof[q]) cudaFree(g.zprof[q]); g.zprof[q] = nullptr; }
+  if (g.comm && g.nccl.CommDestroy) { g.nccl.CommDestroy(g.comm); g.comm = nullptr; }
+  g.have_par = false; g.npartials = 0; g.nranks = 1; g.rank = 0;
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_timer_start(void) { CK(cudaEventRecord(g.ev_t0, g.st)); return PCB200_OK; }
+extern "C" int pcb200_timer_stop(float *ms)
+{
+  CK(cudaEventRecord(g.ev_t1, g.st));
+  CK(cudaEventSynchronize(g.ev_t1));
+  CK(cudaEventElapsedTime(ms, g.ev_t0, g.ev_t1));
+  return PCB200_OK;
+}
+extern "C" int pcb200_sync(void) { CK(cudaStreamSynchronize(g.st)); if (g.st_comm) CK(cudaStreamSynchronize(g.st_comm)); return PCB200_OK; }
+extern "C" int64_t pcb200_launch_count(void) { const int64_t n = g.launches; g.launches = 0; return n; }

@@ -1,0 +1,239 @@
+// physics.cuh -- the fused right-hand side of one grid cell.
+//
+// Replaces, for one (l,m,n), everything the reference evaluates per pencil in
+// rhs_cpu (equ.f90:816-1239): calc_pencils_{hydro,density,eos,energy,viscosity,
+// magnetic} and duu_dt / dlnrho_dt / denergy_dt / daa_dt / duu_dt_grav plus the
+// CFL combination (equ.f90:1086-1151).  The stencils are the 6th-order ones of
+// deriv.f90 (der :89, der2 :474, derij bidiagonal :1373, der6 upwind :938).
+// The data access is abstracted by an accessor `A` so that the same physics
+// serves the z-marching shared-memory kernel and the plain global-memory
+// kernel.  Evaluation order is free here (FMA contraction on): parity with the
+// Fortran order is a 1e-10 tolerance, checked against oracle/pcref.c.
+#pragma once
+#include "devpar.h"
+
+#define PC_DEV __device__ __forceinline__
+
+// ---- stencils ---------------------------------------------------------
+template <int R, class A> PC_DEV double ddx(const A &a, double f1)
+{ return f1 * (45.0 * (a.template x<R, 1>() - a.template x<R, -1>()) - 9.0 * (a.template x<R, 2>() - a.template x<R, -2>()) + (a.template x<R, 3>() - a.template x<R, -3>())); }
+template <int R, class A> PC_DEV double ddy(const A &a, double f1)
+{ return f1 * (45.0 * (a.template y<R, 1>() - a.template y<R, -1>()) - 9.0 * (a.template y<R, 2>() - a.template y<R, -2>()) + (a.template y<R, 3>() - a.template y<R, -3>())); }
+template <int R, class A> PC_DEV double ddz(const A &a, double f1)
+{ return f1 * (45.0 * (a.template z<R, 1>() - a.template z<R, -1>()) - 9.0 * (a.template z<R, 2>() - a.template z<R, -2>()) + (a.template z<R, 3>() - a.template z<R, -3>())); }
+
+#define PC_C0 (-490.0 / 180.0)
+#define PC_C1 (270.0 / 180.0)
+#define PC_C2 (-27.0 / 180.0)
+#define PC_C3 (2.0 / 180.0)
+template <int R, class A> PC_DEV double d2x(const A &a, double f2)
+{ return f2 * (PC_C0 * a.template c<R>() + PC_C1 * (a.template x<R, 1>() + a.template x<R, -1>()) + PC_C2 * (a.template x<R, 2>() + a.template x<R, -2>()) + PC_C3 * (a.template x<R, 3>() + a.template x<R, -3>())); }
+template <int R, class A> PC_DEV double d2y(const A &a, double f2)
+{ return f2 * (PC_C0 * a.template c<R>() + PC_C1 * (a.template y<R, 1>() + a.template y<R, -1>()) + PC_C2 * (a.template y<R, 2>() + a.template y<R, -2>()) + PC_C3 * (a.template y<R, 3>() + a.template y<R, -3>())); }
+template <int R, class A> PC_DEV double d2z(const A &a, double f2)
+{ return f2 * (PC_C0 * a.template c<R>() + PC_C1 * (a.template z<R, 1>() + a.template z<R, -1>()) + PC_C2 * (a.template z<R, 2>() + a.template z<R, -2>()) + PC_C3 * (a.template z<R, 3>() + a.template z<R, -3>())); }
+
+// upwind correction D6 * dx^5/60 (der6 with upwind=T)
+template <int R, class A> PC_DEV double d6x(const A &a, double f1)
+{ return f1 * (-20.0 * a.template c<R>() + 15.0 * (a.template x<R, 1>() + a.template x<R, -1>()) - 6.0 * (a.template x<R, 2>() + a.template x<R, -2>()) + (a.template x<R, 3>() + a.template x<R, -3>())); }
+template <int R, class A> PC_DEV double d6y(const A &a, double f1)
+{ return f1 * (-20.0 * a.template c<R>() + 15.0 * (a.template y<R, 1>() + a.template y<R, -1>()) - 6.0 * (a.template y<R, 2>() + a.template y<R, -2>()) + (a.template y<R, 3>() + a.template y<R, -3>())); }
+template <int R, class A> PC_DEV double d6z(const A &a, double f1)
+{ return f1 * (-20.0 * a.template c<R>() + 15.0 * (a.template z<R, 1>() + a.template z<R, -1>()) - 6.0 * (a.template z<R, 2>() + a.template z<R, -2>()) + (a.template z<R, 3>() + a.template z<R, -3>())); }
+
+// bidiagonal mixed derivatives
+template <int R, class A> PC_DEV double dxy(const A &a, double fij)
+{
+  return fij * (270.0 * (a.template xy<R, 1, 1>() - a.template xy<R, -1, 1>() + a.template xy<R, -1, -1>() - a.template xy<R, 1, -1>())
+                - 27.0 * (a.template xy<R, 2, 2>() - a.template xy<R, -2, 2>() + a.template xy<R, -2, -2>() - a.template xy<R, 2, -2>())
+                + 2.0 * (a.template xy<R, 3, 3>() - a.template xy<R, -3, 3>() + a.template xy<R, -3, -3>() - a.template xy<R, 3, -3>()));
+}
+template <int R, class A> PC_DEV double dxz(const A &a, double fij)
+{
+  return fij * (270.0 * (a.template xz<R, 1, 1>() - a.template xz<R, -1, 1>() + a.template xz<R, -1, -1>() - a.template xz<R, 1, -1>())
+                - 27.0 * (a.template xz<R, 2, 2>() - a.template xz<R, -2, 2>() + a.template xz<R, -2, -2>() - a.template xz<R, 2, -2>())
+                + 2.0 * (a.template xz<R, 3, 3>() - a.template xz<R, -3, 3>() + a.template xz<R, -3, -3>() - a.template xz<R, 3, -3>()));
+}
+template <int R, class A> PC_DEV double dyz(const A &a, double fij)
+{
+  return fij * (270.0 * (a.template yz<R, 1, 1>() - a.template yz<R, -1, 1>() + a.template yz<R, -1, -1>() - a.template yz<R, 1, -1>())
+                - 27.0 * (a.template yz<R, 2, 2>() - a.template yz<R, -2, 2>() + a.template yz<R, -2, -2>() - a.template yz<R, 2, -2>())
+                + 2.0 * (a.template yz<R, 3, 3>() - a.template yz<R, -3, 3>() + a.template yz<R, -3, -3>() - a.template yz<R, 3, -3>()));
+}
+
+// per-cell by-products for the CFL step and the 0-D diagnostics
+struct CellAux {
+  double dt1;        // local inverse time step (equ.f90:1149)
+  double u2, rho, ss, b2, j2, ab, jb, ou;
+  double dtc, dtu, dtnu, dtchi;
+};
+
+// rhs[role] receives dX/dt for each present role.
+// iz = z index of the cell relative to n1 (for the 1-D z profiles).
+template <bool MAG, bool ENT, bool AUX, class A>
+PC_DEV void rhs_cell(const A &a, const DevPar &c, int iz, double *__restrict__ rhs, CellAux &aux)
+{
+  // ---------------- hydro pencils (hydro.f90:2913-3207) ----------------
+  const double ux = a.template c<R_UX>(), uy = a.template c<R_UY>(), uz = a.template c<R_UZ>();
+  const double uxx = ddx<R_UX>(a, c.fx1), uxy = ddy<R_UX>(a, c.fy1), uxz = ddz<R_UX>(a, c.fz1);
+  const double uyx = ddx<R_UY>(a, c.fx1), uyy = ddy<R_UY>(a, c.fy1), uyz = ddz<R_UY>(a, c.fz1);
+  const double uzx = ddx<R_UZ>(a, c.fx1), uzy = ddy<R_UZ>(a, c.fy1), uzz = ddz<R_UZ>(a, c.fz1);
+  const double divu = uxx + uyy + uzz;
+  // traceless rate of strain (sub.f90:8314)
+  const double third = 1.0 / 3.0;
+  const double sxx = uxx - third * divu, syy = uyy - third * divu, szz = uzz - third * divu;
+  const double sxy = 0.5 * (uxy + uyx), sxz = 0.5 * (uxz + uzx), syz = 0.5 * (uyz + uzy);
+  // u.grad u (sub.f90:3227), optional upwinding (sub.f90:6941)
+  double ugux = ux * uxx + uy * uxy + uz * uxz;
+  double uguy = ux * uyx + uy * uyy + uz * uyz;
+  double uguz = ux * uzx + uy * uzy + uz * uzz;
+  const double aux_ = fabs(ux), auy_ = fabs(uy), auz_ = fabs(uz);
+  if (c.lupw_uu) {
+    ugux -= aux_ * d6x<R_UX>(a, c.fx1) + auy_ * d6y<R_UX>(a, c.fy1) + auz_ * d6z<R_UX>(a, c.fz1);
+    uguy -= aux_ * d6x<R_UY>(a, c.fx1) + auy_ * d6y<R_UY>(a, c.fy1) + auz_ * d6z<R_UY>(a, c.fz1);
+    uguz -= aux_ * d6x<R_UZ>(a, c.fx1) + auy_ * d6y<R_UZ>(a, c.fy1) + auz_ * d6z<R_UZ>(a, c.fz1);
+  }
+  // del2 u and grad div u (del2v_etc, sub.f90:2397)
+  const double uxxx = d2x<R_UX>(a, c.fx2), uyyy = d2y<R_UY>(a, c.fy2), uzzz = d2z<R_UZ>(a, c.fz2);
+  const double del2ux = uxxx + d2y<R_UX>(a, c.fy2) + d2z<R_UX>(a, c.fz2);
+  const double del2uy = d2x<R_UY>(a, c.fx2) + uyyy + d2z<R_UY>(a, c.fz2);
+  const double del2uz = d2x<R_UZ>(a, c.fx2) + d2y<R_UZ>(a, c.fy2) + uzzz;
+  const double gdx = uxxx + dxy<R_UY>(a, c.fxy) + dxz<R_UZ>(a, c.fzx);
+  const double gdy = dxy<R_UX>(a, c.fxy) + uyyy + dyz<R_UZ>(a, c.fyz);
+  const double gdz = dxz<R_UX>(a, c.fzx) + dyz<R_UY>(a, c.fyz) + uzzz;
+
+  // ---------------- density pencils (density.f90:2341) ----------------
+  const double lnrho = a.template c<R_LNRHO>();
+  const double rho1 = exp(-lnrho);
+  const double glx = ddx<R_LNRHO>(a, c.fx1), gly = ddy<R_LNRHO>(a, c.fy1), glz = ddz<R_LNRHO>(a, c.fz1);
+  double uglnrho = ux * glx + uy * gly + uz * glz;
+  if (c.lupw_lnrho)
+    uglnrho -= aux_ * d6x<R_LNRHO>(a, c.fx1) + auy_ * d6y<R_LNRHO>(a, c.fy1) + auz_ * d6z<R_LNRHO>(a, c.fz1);
+  const double sglx = sxx * glx + sxy * gly + sxz * glz;
+  const double sgly = sxy * glx + syy * gly + syz * glz;
+  const double sglz = sxz * glx + syz * gly + szz * glz;
+
+  // ---------------- EOS + energy pencils ----------------
+  double cs2 = c.cs20, TT1 = 0.0, ee = 1.0, ss = 0.0;
+  double gTx = 0.0, gTy = 0.0, gTz = 0.0, del2lnTT = 0.0, ugss = 0.0;
+  double fpx, fpy, fpz;
+  if (ENT) {
+    // eos_idealgas.f90:843-868
+    ss = a.template c<R_SS>();
+    const double gsx = ddx<R_SS>(a, c.fx1), gsy = ddy<R_SS>(a, c.fy1), gsz = ddz<R_SS>(a, c.fz1);
+    const double del2ss = d2x<R_SS>(a, c.fx2) + d2y<R_SS>(a, c.fy2) + d2z<R_SS>(a, c.fz2);
+    const double del2lnrho = d2x<R_LNRHO>(a, c.fx2) + d2y<R_LNRHO>(a, c.fy2) + d2z<R_LNRHO>(a, c.fz2);
+    const double th = c.cv1 * ss + c.gamma_m1 * (lnrho - c.lnrho0);
+    const double eth = exp(th);
+    cs2 = c.cs20 * eth;
+    const double lnTT = c.lnTT0 + th;
+    const double TT = exp(lnTT);
+    ee = c.cv * TT;
+    TT1 = 1.0 / TT;
+    gTx = c.gamma_m1 * glx + c.cv1 * gsx; gTy = c.gamma_m1 * gly + c.cv1 * gsy; gTz = c.gamma_m1 * glz + c.cv1 * gsz;
+    del2lnTT = c.gamma_m1 * del2lnrho + c.cv1 * del2ss;
+    ugss = ux * gsx + uy * gsy + uz * gsz;                         // entropy.f90:3189
+    if (c.lupw_ss)
+      ugss -= aux_ * d6x<R_SS>(a, c.fx1) + auy_ * d6y<R_SS>(a, c.fy1) + auz_ * d6z<R_SS>(a, c.fz1);
+    const double pf = -cs2 * c.gamma1;                             // entropy.f90:3209
+    fpx = pf * (glx + gTx); fpy = pf * (gly + gTy); fpz = pf * (glz + gTz);
+  } else {
+    fpx = -cs2 * glx; fpy = -cs2 * gly; fpz = -cs2 * glz;          // noentropy.f90:291
+  }
+
+  // ---------------- momentum (hydro.f90:3704, viscosity.f90:1421-1448,2571) ----------------
+  double dux = -ugux + c.Omega2 * uy + c.nu * (del2ux + 2.0 * sglx + third * gdx) + fpx;
+  double duy = -uguy - c.Omega2 * ux + c.nu * (del2uy + 2.0 * sgly + third * gdy) + fpy;
+  double duz = -uguz + c.nu * (del2uz + 2.0 * sglz + third * gdz) + fpz;
+  if (c.lgravz) duz += c.gravz;                                    // gravity_simple.f90:914
+
+  // ---------------- continuity (density.f90:2542-2623) ----------------
+  rhs[R_LNRHO] = -divu - uglnrho;
+
+  const double sij2 = sxx * sxx + syy * syy + szz * szz + 2.0 * (sxy * sxy + sxz * sxz + syz * syz);
+  double advec_va2 = 0.0, j2 = 0.0, b2 = 0.0, ab = 0.0, jb = 0.0;
+
+  // ---------------- magnetic (magnetic.f90:3587-3990, 4229-5589) ----------------
+  if (MAG) {
+    const double axy = ddy<R_AX>(a, c.fy1), axz = ddz<R_AX>(a, c.fz1);
+    const double ayx = ddx<R_AY>(a, c.fx1), ayz = ddz<R_AY>(a, c.fz1);
+    const double azx = ddx<R_AZ>(a, c.fx1), azy = ddy<R_AZ>(a, c.fy1);
+    const double bx = azy - ayz, by = axz - azx, bz = ayx - axy;   // curl_mn
+    b2 = bx * bx + by * by + bz * bz;
+    // second derivatives (gij_etc, sub.f90:2732): del2 A and J = curl curl A / mu0
+    const double axxx = d2x<R_AX>(a, c.fx2), axyy = d2y<R_AX>(a, c.fy2), axzz = d2z<R_AX>(a, c.fz2);
+    const double ayxx = d2x<R_AY>(a, c.fx2), ayyy = d2y<R_AY>(a, c.fy2), ayzz = d2z<R_AY>(a, c.fz2);
+    const double azxx = d2x<R_AZ>(a, c.fx2), azyy = d2y<R_AZ>(a, c.fy2), azzz = d2z<R_AZ>(a, c.fz2);
+    const double del2ax = axxx + axyy + axzz, del2ay = ayxx + ayyy + ayzz, del2az = azxx + azyy + azzz;
+    // jj(1)=bij(3,2)-bij(2,3) etc. with bij(i,l)=eps d2A (sub.f90:2773-2781, magnetic.f90:3787)
+    const double jx = c.mu01 * ((dxy<R_AY>(a, c.fxy) - axyy) - (axzz - dxz<R_AZ>(a, c.fzx)));
+    const double jy = c.mu01 * ((dyz<R_AZ>(a, c.fyz) - ayzz) - (ayxx - dxy<R_AX>(a, c.fxy)));
+    const double jz = c.mu01 * ((dxz<R_AX>(a, c.fzx) - azxx) - (azyy - dyz<R_AY>(a, c.fyz)));
+    j2 = jx * jx + jy * jy + jz * jz;
+    // Lorentz force J x B / rho (magnetic.f90:4360)
+    dux += rho1 * (jy * bz - jz * by);
+    duy += rho1 * (jz * bx - jx * bz);
+    duz += rho1 * (jx * by - jy * bx);
+    // induction: dA/dt = u x B + eta del2 A (magnetic.f90:4399,5238,5521)
+    rhs[R_AX] = (uy * bz - uz * by) + c.eta * del2ax;
+    rhs[R_AY] = (uz * bx - ux * bz) + c.eta * del2ay;
+    rhs[R_AZ] = (ux * by - uy * bx) + c.eta * del2az;
+    const double t0 = bx * c.dx_1, t1 = by * c.dy_1, t2 = bz * c.dz_1;
+    advec_va2 = (t0 * t0 + t1 * t1 + t2 * t2) * c.mu01 * rho1;    // magnetic.f90:5438
+    if (AUX) {
+      const double ax = a.template c<R_AX>(), ay = a.template c<R_AY>(), az = a.template c<R_AZ>();
+      ab = ax * bx + ay * by + az * bz;
+      jb = jx * bx + jy * by + jz * bz;
+    }
+  }
+  rhs[R_UX] = dux; rhs[R_UY] = duy; rhs[R_UZ] = duz;
+
+  // ---------------- entropy equation (entropy.f90:3242-3452) ----------------
+  double Hmax = 0.0, diffus_chi = 0.0;
+  if (ENT) {
+    double dss = -ugss;
+    const double visc_heat = 2.0 * c.nu * sij2;                    // viscosity.f90:1447
+    if (c.lviscosity_heat) { dss += TT1 * visc_heat; Hmax += visc_heat; }
+    if (c.iheatcond == PCB200_HCOND_KPROFILE) {                    // calc_heatcond :5333
+      const double hcond = c.zprof[PCB200_PROF_HCOND][iz];
+      const double glhc = c.zprof[PCB200_PROF_DLNHCOND][iz];
+      const double g2 = gTx * gTx + gTy * gTy + gTz * (gTz + glhc);
+      dss += rho1 * hcond * (del2lnTT + g2);
+      diffus_chi += c.gamma * (rho1 * hcond * c.cp1) * c.dxyz_2;
+    } else if (c.iheatcond == PCB200_HCOND_CHICONST) {             // calc_heatcond_constchi :4266
+      const double g2 = (glx + gTx) * gTx + (gly + gTy) * gTy + (glz + gTz) * gTz;
+      dss += c.chi * c.cp * (del2lnTT + g2);
+      diffus_chi += (c.gamma * c.chi) * c.dxyz_2;
+    }
+    if (c.lcooling) {                                              // get_heat_cool_gravz :6196
+      const double heat = -c.cool * c.zprof[PCB200_PROF_COOL][iz] * (cs2 - c.cs2cool) / c.cs2cool;
+      dss += TT1 * rho1 * heat;
+      Hmax += heat * rho1;
+    }
+    if (MAG && c.lohmic_heat) dss += c.eta * c.mu0 * j2 * rho1 * TT1;   // magnetic.f90:5127
+    rhs[R_SS] = dss;
+  }
+
+  // ---------------- time-step constraint (equ.f90:1086-1151) ----------------
+  if (AUX) {
+    const double advec_uu = aux_ * c.dx_1 + auy_ * c.dy_1 + auz_ * c.dz_1;      // hydro.f90:3810
+    const double advec_cs2 = cs2 * c.dxyz_2;
+    const double maxadvec = advec_uu + sqrt(advec_va2 + advec_cs2);
+    double maxdiffus = c.nu * c.dxyz_2;
+    if (MAG) maxdiffus = fmax(maxdiffus, c.eta * c.dxyz_2);
+    if (ENT) maxdiffus = fmax(maxdiffus, diffus_chi);
+    const double dt1_advec = maxadvec / c.cdt, dt1_diffus = maxdiffus / c.cdtv;
+    double dt1 = sqrt(dt1_advec * dt1_advec + dt1_diffus * dt1_diffus);
+    if (ENT) dt1 = fmax(dt1, fabs(Hmax / ee / c.cdts));                          // entropy.f90:3444
+    aux.dt1 = dt1;
+    aux.u2 = ux * ux + uy * uy + uz * uz;
+    aux.rho = 1.0 / rho1;
+    aux.ss = ss;
+    aux.b2 = b2; aux.j2 = j2; aux.ab = ab; aux.jb = jb;
+    aux.ou = (uzy - uyz) * ux + (uxz - uzx) * uy + (uyx - uxy) * uz;
+    aux.dtc = sqrt(advec_cs2) / c.cdt;
+    aux.dtu = advec_uu / c.cdt;
+    aux.dtnu = c.nu * c.dxyz_2 / c.cdtv;
+    aux.dtchi = diffus_chi / c.cdtv;
+  }
+}
