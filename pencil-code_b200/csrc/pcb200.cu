@@ -51,7 +51,7 @@ struct Ctx {
   double *dt_dev = nullptr;     // [0]=dt [1]=dt1
   double *pinned = nullptr;     // [NRED+2]
   double *zprof[PCB200_NPROF] = {nullptr, nullptr, nullptr};
-  double *f_host = nullptr;
+  double *f_host = nullptr; bool f_host_pinned = false;
   bool have_forcing = false; pcb200_forcing frc;
   double dt = 0.0;
   double diag[PCB200_NDIAG];
@@ -106,7 +106,7 @@ static void free_fields()
 {
   for (int i = 0; i < 2; i++) { if (g.f[i]) cudaFree(g.f[i]); g.f[i] = nullptr; }
   if (g.w) cudaFree(g.w); g.w = nullptr;
-  if (g.partials) cudaFree(g.partials); g.partials = nullptr;
+  if (g.partials) cudaFree(g.partials); g.partials = nullptr; g.npartials = 0;
 }
 
 extern "C" int pcb200_initialize(const pcb200_params *par)
@@ -204,8 +204,21 @@ extern "C" int pcb200_set_zprofile(int which, const double *prof, int nz)
 extern "C" int pcb200_register(double *f_host)
 {
   if (!f_host) return fail(PCB200_EARG, "null f");
+  if (g.f_host_pinned && g.f_host != f_host) { cudaHostUnregister(g.f_host); g.f_host_pinned = false; }
   g.f_host = f_host;      // aliased only (astaroth/gpu_astaroth.cc:224-234)
   return PCB200_OK;
+}
+
+// page-lock the registered host array once so that uploads/downloads run at
+// full PCIe rate (the reference notes this as time-critical, astaroth/loadStore.cc:82)
+static void pin_registered()
+{
+  if (g.f_host && !g.f_host_pinned && g.nelem) {
+    const char *e = getenv("PCB200_PIN_HOST");
+    if (e && !atoi(e)) return;
+    if (cudaHostRegister(g.f_host, g.nelem * sizeof(double), cudaHostRegisterDefault) == cudaSuccess) g.f_host_pinned = true;
+    else cudaGetLastError();   // not fatal: fall back to pageable copies
+  }
 }
 
 extern "C" int pcb200_load_farray(const double *f_host)
@@ -213,6 +226,7 @@ extern "C" int pcb200_load_farray(const double *f_host)
   if (!g.have_par) return fail(PCB200_ESTATE, "pcb200_load_farray before pcb200_initialize");
   const double *src = f_host ? f_host : g.f_host;
   if (!src) return fail(PCB200_ESTATE, "no host array registered");
+  if (src == g.f_host) pin_registered();
   CK(cudaMemcpyAsync(g.f[g.cur], src, g.nelem * sizeof(double), cudaMemcpyHostToDevice, g.st));
   CK(cudaStreamSynchronize(g.st));
   return PCB200_OK;
@@ -458,6 +472,7 @@ extern "C" int pcb200_copy_farray(double *f_host)
   double *dst = f_host ? f_host : g.f_host;
   if (!dst) return fail(PCB200_ESTATE, "no host array registered");
   CK(cudaSetDevice(g.dev));
+  if (dst == g.f_host) pin_registered();
   CK(cudaMemcpyAsync(dst, g.f[g.cur], g.nelem * sizeof(double), cudaMemcpyDeviceToHost, g.st));
   CK(cudaStreamSynchronize(g.st));
   return PCB200_OK;
@@ -504,6 +519,8 @@ extern "C" int pcb200_finalize(void)
   cudaSetDevice(g.dev);
   cudaStreamSynchronize(g.st);
   free_fields();
+  if (g.f_host_pinned) { cudaHostUnregister(g.f_host); g.f_host_pinned = false; }
+  g.f_host = nullptr;
   for (int q = 0; q < PCB200_NPROF; q++) { if (g.zprof[q]) cudaFree(g.zprof[q]); g.zprof[q] = nullptr; }
   if (g.comm && g.nccl.CommDestroy) { g.nccl.CommDestroy(g.comm); g.comm = nullptr; }
   g.have_par = false; g.npartials = 0; g.nranks = 1; g.rank = 0;

@@ -1,0 +1,200 @@
+"""Run set-ups for the hot path: what start.in/run.in + cparam.local resolve to
+for the BASELINE configs, as a Params block, plus the
+deterministic synthetic initial fields of SURVEY.md section 8(d).
+
+The numbers mirror the reference's shipped inputs:
+  conv-slab        samples/conv-slab/{start.in,run.in,src/cparam.local}
+  helical-MHDturb  samples/helical-MHDturb/{start.in,run.in}
+Defaults: cdata.f90:145-153 (cdt,cdtv,cdts,dtmax), timestep.f90:40-41.
+"""
+import math
+
+import numpy as np
+
+from . import abi
+
+NG = abi.NGHOST
+
+
+def grid_axis(n, x0, L, periodic):
+    """Equidistant grid incl. ghosts (grid.f90:118-222): periodic xi=0.5..N-0.5,
+    dx=L/N; non-periodic xi=0..N-1, dx=L/(N-1)."""
+    dx = L / n if periodic else L / max(n - 1, 1)
+    xi = np.arange(-NG, n + NG, dtype=np.float64) + (0.5 if periodic else 0.0)
+    return x0 + dx * xi, dx
+
+
+def make_params(nxgrid, nygrid, nzgrid, *, magnetic=False, entropy=False, xyz0=(-math.pi,) * 3,
+                Lxyz=(2 * math.pi,) * 3, lperi=(1, 1, 1), nprocz=1, ipz=0, **kw):
+    """Build (Params, zprofiles, grid) for a z-slab of the global grid."""
+    P = abi.Params()
+    P.abi_version = abi.ABI_VERSION
+    assert nzgrid % nprocz == 0
+    nz = nzgrid // nprocz
+    P.nx, P.ny, P.nz = nxgrid, nygrid, nz
+    P.nprocx, P.nprocy, P.nprocz = 1, 1, nprocz
+    P.ipx, P.ipy, P.ipz = 0, 0, ipz
+    for i in range(3):
+        P.lperi[i] = int(lperi[i])
+        P.xyz0[i] = xyz0[i]
+        P.Lxyz[i] = Lxyz[i]
+    # variable slots in registration order (register.f90:124-135)
+    P.iux, P.iuy, P.iuz, P.ilnrho = 1, 2, 3, 4
+    nv = 4
+    if entropy:
+        nv += 1
+        P.iss = nv
+    if magnetic:
+        P.iax, P.iay, P.iaz = nv + 1, nv + 2, nv + 3
+        nv += 3
+    P.mvar = P.mfarray = nv
+    P.lhydro = P.ldensity = 1
+    P.lentropy, P.lmagnetic = int(entropy), int(magnetic)
+    P.lbidiagonal_derij = 1
+    P.lviscosity_heat = 1
+    P.lohmic_heat = 1
+    P.ldt = 1
+    x, dx = grid_axis(nxgrid, xyz0[0], Lxyz[0], lperi[0])
+    y, dy = grid_axis(nygrid, xyz0[1], Lxyz[1], lperi[1])
+    zg, dz = grid_axis(nzgrid, xyz0[2], Lxyz[2], lperi[2])
+    z = zg[ipz * nz: ipz * nz + nz + 2 * NG].copy()
+    P.dx, P.dy, P.dz = dx, dy, dz
+    P.dx_1, P.dy_1, P.dz_1 = 1.0 / dx, 1.0 / dy, 1.0 / dz
+    for i in range(1, NG + 1):          # grid.f90:2670-2672
+        P.dz2_bound[3 - i] = 2.0 * (z[NG + i] - z[NG])
+        P.dz2_bound[3 + i] = 2.0 * (z[NG + nz - 1] - z[NG + nz - 1 - i])
+    P.x0_loc, P.y0_loc, P.z0_loc = x[NG], y[NG], z[NG]
+    P.cdt, P.cdtv, P.cdts, P.dtmax = 0.9, 0.25, 1.0, 1e37
+    P.alpha_ts[0], P.alpha_ts[1], P.alpha_ts[2] = 0.0, -5 / 9.0, -153 / 128.0
+    P.beta_ts[0], P.beta_ts[1], P.beta_ts[2] = 1 / 3.0, 15 / 16.0, 8 / 15.0
+    P.mu0 = 1.0
+    P.cs20, P.gamma, P.cp, P.lnrho0 = 1.0, (5.0 / 3.0 if entropy else 1.0), 1.0, 0.0
+    P.ztop = xyz0[2] + Lxyz[2]
+    for name, val in kw.items():
+        if name in ("bcx", "bcy", "bcz"):
+            continue
+        if not hasattr(P, name):
+            raise KeyError(name)
+        setattr(P, name, val)
+    for axis in ("bcx", "bcy", "bcz"):
+        spec = kw.get(axis)
+        arr = getattr(P, axis)
+        for k in range(abi.MAXVAR):
+            lo = hi = "p"
+            if spec is not None and k < len(spec):
+                s = spec[k]
+                lo, hi = s.split(":") if ":" in s else (s, s)
+            arr[0][k] = abi.BC[lo]
+            arr[1][k] = abi.BC[hi]
+    grid = dict(x=x, y=y, z=z, zglobal=zg, dx=dx, dy=dy, dz=dz)
+    zprof = {}
+    if entropy:
+        zprof = entropy_zprofiles(P, z[NG:NG + nz])
+    return P, zprof, grid
+
+
+def _step(x, x0, width):          # sub.f90:4544 step_vector
+    tini = np.finfo(np.float64).tiny * 5
+    return 0.5 * (1 + np.tanh((x - x0) / (width + tini)))
+
+
+def _der_step(x, x0, width):      # sub.f90 der_step
+    tini = np.finfo(np.float64).tiny * 5
+    arg = np.abs((x - x0) / (width + tini))
+    return np.where(arg >= 8.0, 2.0 / width * np.exp(-2.0 * arg), 0.5 / (width * np.cosh(np.minimum(arg, 8.0)) ** 2))
+
+
+def entropy_zprofiles(P, z):
+    """hcond_prof, dlnhcond_prof (get_gravz_heatcond, entropy.f90:7243-7262) and the
+    'gaussian' cooling profile of get_heat_cool_gravz (entropy.f90:6244)."""
+    out = {}
+    if P.iheatcond == abi.HCOND["K-profile"]:
+        prof = 1.0 + (P.hcond1 - 1.0) * _step(z, P.z1, -P.widthss) + (P.hcond2 - 1.0) * _step(z, P.z2, P.widthss)
+        dln = ((P.hcond1 - 1.0) * _der_step(z, P.z1, -P.widthss) + (P.hcond2 - 1.0) * _der_step(z, P.z2, P.widthss)) / prof
+        out[abi.PROF_HCOND] = P.hcond0 * prof
+        out[abi.PROF_DLNHCOND] = dln
+    if P.lcooling:
+        out[abi.PROF_COOL] = np.exp(-0.5 * ((P.ztop - z) / P.wcool) ** 2)
+    return out
+
+
+# --------------------------------------------------------------------------
+# synthetic smooth fields, seed 12345
+# --------------------------------------------------------------------------
+def _mode_sum(rng, grid, nmodes, kmax, ampl, Lxyz, xyz0):
+    """sum_i a_i cos(k_i.(x-x0) + phi_i), k_i integer multiples of 2pi/L: periodic
+    on the box, evaluated on the ghost-padded grid (ghosts consistent)."""
+    x, y, z = grid["x"], grid["y"], grid["z"]
+    acc = np.zeros((z.size, y.size, x.size))
+    k = rng.integers(-kmax, kmax + 1, size=(nmodes, 3))
+    k[(k == 0).all(axis=1)] = (1, 0, 0)
+    a = rng.standard_normal(nmodes) / math.sqrt(nmodes)
+    phi = rng.uniform(0, 2 * math.pi, nmodes)
+    ex = np.exp(1j * np.outer(k[:, 0] * 2 * math.pi / Lxyz[0], x - xyz0[0]))
+    ey = np.exp(1j * np.outer(k[:, 1] * 2 * math.pi / Lxyz[1], y - xyz0[1]))
+    ez = np.exp(1j * np.outer(k[:, 2] * 2 * math.pi / Lxyz[2], z - xyz0[2])) * (a * np.exp(1j * phi))[:, None]
+    exy = (ey[:, :, None] * ex[:, None, :]).reshape(nmodes, -1)        # [i, y*x]
+    acc = (ez.T.real @ exy.real - ez.T.imag @ exy.imag).reshape(z.size, y.size, x.size)
+    return ampl * acc
+
+
+def synthetic_fields(P, grid, seed=12345, ampl_u=0.1, ampl_lnrho=0.1, ampl_a=1e-2, ampl_ss=0.05):
+    """f(mvar,mz,my,mx) C-ordered == Fortran f(mx,my,mz,mvar)."""
+    rng = np.random.default_rng(seed)
+    L = [P.Lxyz[i] for i in range(3)]
+    x0 = [P.xyz0[i] for i in range(3)]
+    mx, my, mz = P.nx + 2 * NG, P.ny + 2 * NG, P.nz + 2 * NG
+    f = np.zeros((P.mvar, mz, my, mx))
+    # the random draws are made in a fixed order so that every rank of a
+    # decomposed run generates the same global field
+    for j in range(3):
+        f[P.iux - 1 + j] = _mode_sum(rng, grid, 16, 4, ampl_u, L, x0)
+    f[P.ilnrho - 1] = _mode_sum(rng, grid, 8, 3, ampl_lnrho, L, x0)
+    if P.lentropy:
+        f[P.iss - 1] = _mode_sum(rng, grid, 8, 3, ampl_ss, L, x0)
+    if P.lmagnetic:
+        for j in range(3):
+            f[P.iax - 1 + j] = _mode_sum(rng, grid, 16, 8, ampl_a, L, x0)
+    return f
+
+
+def config_hydro(n=64, **kw):
+    """BASELINE config 2: periodic isothermal hydro (forcing optional)."""
+    d = dict(nu=5e-3, cdt=0.4, cdtv=0.3)
+    d.update(kw)
+    return make_params(n, n, n, **d)
+
+
+def config_mhd(n=64, nprocz=1, ipz=0, **kw):
+    """BASELINE config 3: isothermal helical MHD (samples/helical-MHDturb/run.in:
+    cdt=0.4, cdtv=0.3, eta=nu=5e-3)."""
+    d = dict(nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3)
+    d.update(kw)
+    return make_params(n, n, n, magnetic=True, nprocz=nprocz, ipz=ipz, **d)
+
+
+def config_mhd_entropy(n=64, nprocz=1, ipz=0, **kw):
+    """BASELINE config 4: MHD + entropy, iheatcond='chi-const' (SURVEY A.5)."""
+    d = dict(nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3, chi=1e-4, iheatcond=abi.HCOND["chi-const"])
+    d.update(kw)
+    return make_params(n, n, n, magnetic=True, entropy=True, nprocz=nprocz, ipz=ipz, **d)
+
+
+def config_convslab(nxgrid=32, nygrid=32, nzgrid=32, nprocz=1, ipz=0, **kw):
+    """BASELINE config 1: samples/conv-slab (start.in, run.in)."""
+    gamma = 1.6666666
+    cs0 = 0.57735
+    hcond0, mpoly0, mpoly1, mpoly2, gravz = 8e-3, 1.0, 3.0, 0.0, -1.0
+    d = dict(
+        xyz0=(-0.5, -0.5, -0.68), Lxyz=(1.0, 1.0, 2.0), lperi=(1, 1, 0),
+        nu=4e-3, cdt=0.4, cdtv=0.3, Omega=0.1, lgravz=1, gravz=gravz,
+        lupw_lnrho=1, lupw_ss=1, cs20=cs0 ** 2, gamma=gamma,
+        iheatcond=abi.HCOND["K-profile"], hcond0=hcond0,
+        hcond1=(mpoly1 + 1.0) / (mpoly0 + 1.0), hcond2=(mpoly2 + 1.0) / (mpoly0 + 1.0),
+        z1=0.0, z2=1.0, widthss=0.05, lcooling=1, cool=15.0, wcool=0.2, cs2cool=0.333333,
+        cs2top=0.333333,
+        Fbot=-gamma / (gamma - 1) * hcond0 * gravz / (mpoly0 + 1),          # entropy.f90:716
+        bcz=["s", "s", "a", "a2", "c1:cT"],
+    )
+    d.update(kw)
+    return make_params(nxgrid, nygrid, nzgrid, entropy=True, nprocz=nprocz, ipz=ipz, **d)

@@ -1,0 +1,150 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.
+
+Tolerances: the north star asks for <=1e-10 relative L-inf after 100 RK3 steps
+in double precision; single substeps / steps are held to 1e-12 (the GPU path
+uses FMA contraction and a different association, the oracle the Fortran
+order)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+INT = (slice(None), slice(3, -3), slice(3, -3), slice(3, -3))
+
+
+def relerr(a, b):
+    """per-variable relative L-inf over the interior, max over variables"""
+    e = 0.0
+    for k in range(a.shape[0]):
+        den = np.abs(b[k][INT[1:]]).max()
+        num = np.abs(a[k][INT[1:]] - b[k][INT[1:]]).max()
+        e = max(e, num / den if den > 0 else num)
+    return e
+
+
+def run_gpu(dev, P, zprof, f0, nsteps, frc=None, diag=False):
+    dev.initialize_GPU(P, zprof)
+    f = f0.copy()
+    dev.register_GPU(f)
+    dev.set_forcing(frc)
+    dts, diags = [], []
+    for _ in range(nsteps):
+        for isub in (1, 2, 3):
+            dt = dev.rhs_GPU(f, isub, ldiagnos=(diag and isub == 1))
+        dts.append(dt)
+        if diag:
+            diags.append(dev.diagnostics())
+    dev.copy_farray_from_GPU(f)
+    dev.set_forcing(None)
+    return f, np.array(dts), diags
+
+
+def run_oracle(orc, P, zprof, f0, nsteps, frc=None, diag=False):
+    orc.set_zprofiles(zprof)
+    f = f0.copy()
+    df = np.zeros_like(f)
+    dts, diags = [], []
+    dt = 0.0
+    for _ in range(nsteps):
+        d = np.zeros(16) if diag else None
+        dt = orc.timestep(f, df, P, dt, frc, d)
+        dts.append(dt)
+        if diag:
+            diags.append(d)
+    return f, np.array(dts), diags
+
+
+CASES = {
+    "hydro": lambda pk: pk.setups.config_hydro(32),
+    "mhd": lambda pk: pk.setups.config_mhd(32),
+    "mhd_entropy": lambda pk: pk.setups.config_mhd_entropy(32),
+    "mhd_ragged": lambda pk: pk.setups.make_params(40, 20, 12, magnetic=True, nu=5e-3, eta=4e-3, cdt=0.4, cdtv=0.3),
+    "hydro_upwind": lambda pk: pk.setups.config_hydro(32, lupw_lnrho=1, lupw_uu=1),
+    "convslab": lambda pk: pk.setups.config_convslab(32, 32, 32),
+}
+
+
+@pytest.mark.parametrize("case", list(CASES))
+def test_one_step_matches_oracle(pk, orc, dev, case):
+    P, zprof, grid = CASES[case](pk)
+    f0 = pk.setups.synthetic_fields(P, grid)
+    if case == "convslab":
+        f0[P.ilnrho - 1] *= 0.1
+    fg, dtg, _ = run_gpu(dev, P, zprof, f0, 1)
+    fo, dto, _ = run_oracle(orc, P, zprof, f0, 1)
+    assert abs(dtg[0] - dto[0]) <= 1e-13 * dto[0]
+    assert relerr(fg, fo) < 1e-12
+
+
+@pytest.mark.parametrize("case", ["mhd", "convslab", "mhd_entropy"])
+def test_global_kernel_matches_march_kernel(pk, orc, dev, case, monkeypatch):
+    """the plain global-memory kernel (boundary slabs) gives the same answer"""
+    import subprocess, sys, os
+    code = f"""
+import sys; sys.path.insert(0, {os.getcwd()!r})
+import numpy as np, __graft_entry__ as g
+pk = g.package()
+import tests.test_gpu_parity as T
+P, zp, grid = T.CASES[{case!r}](pk)
+f0 = pk.setups.synthetic_fields(P, grid)
+d = pk.GPU(); d.gpu_init(0)
+f, dt, _ = T.run_gpu(d, P, zp, f0, 2)
+np.save(sys.argv[1], f)
+"""
+    import tempfile
+    out = {}
+    for kern in ("march", "global"):
+        with tempfile.NamedTemporaryFile(suffix=".npy") as tf:
+            env = dict(os.environ, PCB200_KERNEL=kern)
+            subprocess.check_call([sys.executable, "-c", code, tf.name], env=env)
+            out[kern] = np.load(tf.name)
+    assert relerr(out["global"], out["march"]) < 1e-13
+
+
+@pytest.mark.parametrize("case", ["hydro", "mhd", "mhd_entropy", "convslab"])
+def test_100_steps_within_1e10(pk, orc, dev, case):
+    """north-star bar: <=1e-10 relative L-inf after 100 RK3 steps, dt sequence equal"""
+    P, zprof, grid = CASES[case](pk)
+    f0 = pk.setups.synthetic_fields(P, grid)
+    if case == "convslab":
+        f0[P.ilnrho - 1] *= 0.1
+    fg, dtg, _ = run_gpu(dev, P, zprof, f0, 100)
+    fo, dto, _ = run_oracle(orc, P, zprof, f0, 100)
+    assert np.all(np.isfinite(fg))
+    assert np.abs(dtg / dto - 1).max() <= 1e-11
+    assert relerr(fg, fo) <= 1e-10
+
+
+def test_forcing_and_diagnostics(pk, orc, dev):
+    P, zprof, grid = pk.setups.config_mhd(32)
+    f0 = pk.setups.synthetic_fields(P, grid)
+    frc = pk.abi.Forcing()
+    for j in range(3):
+        frc.coef1[j] = [0.3, -0.2, 0.5][j]
+        frc.coef2[j] = [0.1, 0.4, -0.3][j]
+        frc.fda[j] = 1.0
+        frc.kk[j] = [2.0, -1.0, 3.0][j]
+    frc.phase, frc.fact = 0.7, 0.02
+    fg, dtg, dg = run_gpu(dev, P, zprof, f0, 3, frc, diag=True)
+    fo, dto, do = run_oracle(orc, P, zprof, f0, 3, frc, diag=True)
+    assert relerr(fg, fo) < 1e-12
+    names = pk.abi.DIAG_NAMES
+    for a, b in zip(dg, do):
+        for q, nm in enumerate(names):
+            assert abs(a[nm] - b[q]) <= 1e-11 * max(abs(b[q]), 1e-300), (nm, a[nm], b[q])
+
+
+def test_fixed_dt(pk, orc, dev):
+    P, zprof, grid = pk.setups.config_mhd(32, ldt=0, dt_fixed=1e-3)
+    f0 = pk.setups.synthetic_fields(P, grid)
+    fg, dtg, _ = run_gpu(dev, P, zprof, f0, 2)
+    fo, dto, _ = run_oracle(orc, P, zprof, f0, 2)
+    assert dtg[0] == 1e-3 and dto[0] == 1e-3
+    assert relerr(fg, fo) < 1e-12
+
+
+def test_unsupported_is_refused(pk, dev):
+    P, zprof, grid = pk.setups.config_mhd(32)
+    P.lbidiagonal_derij = 0
+    with pytest.raises(pk.PCB200Error):
+        dev.initialize_GPU(P, zprof)
