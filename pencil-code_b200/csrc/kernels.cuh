@@ -310,19 +310,25 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_march(SubstepArgs a)
     for (int k = 0; k < 7; k++) acc.so[k] = ((q0 + k) & (NSLOT - 1)) * PE;
     acc.po = (q0 & 1) * PE;
     if (active) {
+      const long long idx = (long long)(n + NG) * c.sz + col;
+      // old 2N register: issued before the RHS so that its latency hides behind the stencils
+      double wold[NROLE];
+#pragma unroll
+      for (int r = 0; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        wold[r] = a.alpha != 0.0 ? __ldcs(a.w + idx + (long long)c.slot[r] * c.mw) : 0.0;
+      }
       double rhs[NROLE];
       CellAux aux;
       rhs_cell<MAG, ENT, (AUXM > 0)>(acc, c, n, rhs, aux);
-      const long long idx = (long long)(n + NG) * c.sz + col;
       // 3. 2N-RK3 update (timestep.f90:119-122,162-163); f_in(cell) is the window centre
 #pragma unroll
       for (int r = 0; r < NROLE; r++) {
         if (!role_present<MAG, ENT>(r)) continue;
         const long long i = idx + (long long)c.slot[r] * c.mw;
-        double wv = rhs[r];
-        if (a.alpha != 0.0) wv += a.alpha * a.w[i];
-        if (a.write_w) a.w[i] = wv;
-        if (a.write_f) a.f_out[i] = acc.w[r][3] + beta_dt * wv;
+        const double wv = rhs[r] + a.alpha * wold[r];
+        if (a.write_w) __stcs(a.w + i, wv);
+        if (a.write_f) __stcs(a.f_out + i, acc.w[r][3] + beta_dt * wv);
       }
       if (AUXM > 0) {
         red[RD_DT1] = fmax(red[RD_DT1], aux.dt1);
