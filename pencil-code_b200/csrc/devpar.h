@@ -14,6 +14,7 @@ struct DevPar {
   long long sy, sz, mw;          // strides (elements): y, z, variable
   int mvar;
   int slot[NROLE];               // role -> storage slot, -1 = absent
+  long long foff[NROLE];         // slot*mw: element offset of the role's variable
   int lupw_uu, lupw_lnrho, lupw_ss;
   int iheatcond, lcooling, lviscosity_heat, lohmic_heat, lgravz, ldensity, lhydro;
   double dx_1, dy_1, dz_1;       // 0 for degenerate directions

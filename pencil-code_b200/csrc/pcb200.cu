@@ -56,6 +56,8 @@ struct Ctx {
   double dt = 0.0;
   double diag[PCB200_NDIAG];
   bool use_global = false;      // PCB200_KERNEL=global
+  bool use_march1 = false;      // PCB200_KERNEL=march1 (non-specialised marching kernel also for MHD)
+  bool zwin = true;             // PCB200_ZWIN=0: z neighbours of ring fields from shared memory
   int zchunk = 0;
   int64_t launches = 0;
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
@@ -95,6 +97,9 @@ extern "C" int pcb200_init(int local_rank)
     CK(cudaMallocHost(&g.pinned, sizeof(double) * (NRED + 2)));
     const char *k = getenv("PCB200_KERNEL");
     g.use_global = k && !strcmp(k, "global");
+    g.use_march1 = k && !strcmp(k, "march1");
+    const char *zw = getenv("PCB200_ZWIN");
+    if (zw) g.zwin = atoi(zw) != 0;
     const char *t = getenv("PCB200_TIME_RHS");
     g.time_rhs = t && atoi(t) != 0;
     g.inited = true;
@@ -136,6 +141,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   if (P.lentropy) h.slot[R_SS] = P.iss - 1;
   if (P.lmagnetic) { h.slot[R_AX] = P.iax - 1; h.slot[R_AY] = P.iay - 1; h.slot[R_AZ] = P.iaz - 1; }
   for (int r = 0; r < NROLE; r++) if (h.slot[r] >= P.mvar) return fail(PCB200_EARG, "variable slot beyond mvar");
+  for (int r = 0; r < NROLE; r++) h.foff[r] = h.slot[r] >= 0 ? (long long)h.slot[r] * h.mw : 0;
   h.lupw_uu = P.lupw_uu; h.lupw_lnrho = P.lupw_lnrho; h.lupw_ss = P.lupw_ss;
   h.iheatcond = P.iheatcond; h.lcooling = P.lcooling; h.lviscosity_heat = P.lviscosity_heat; h.lohmic_heat = P.lohmic_heat;
   h.lgravz = P.lgravz; h.ldensity = P.ldensity; h.lhydro = P.lhydro;
@@ -187,6 +193,12 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   OPTIN(false, true, 0);  OPTIN(false, true, 1);  OPTIN(false, true, 2);
   OPTIN(true, true, 0);   OPTIN(true, true, 1);   OPTIN(true, true, 2);
 #undef OPTIN
+#define OPTIN2(E, A, Z) CK(cudaFuncSetAttribute(rhs_march2<E, A, Z>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)March2Cfg<E, A>::SMEM))
+  OPTIN2(false, 0, true); OPTIN2(false, 1, true); OPTIN2(false, 2, true);
+  OPTIN2(true, 0, true);  OPTIN2(true, 1, true);  OPTIN2(true, 2, true);
+  OPTIN2(false, 0, false); OPTIN2(false, 1, false); OPTIN2(false, 2, false);
+  OPTIN2(true, 0, false);  OPTIN2(true, 1, false);  OPTIN2(true, 2, false);
+#undef OPTIN2
   CK(cudaStreamSynchronize(g.st));
   g.have_par = true;
   return PCB200_OK;
@@ -326,6 +338,15 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     else if (M) rhs_global<true, false, AUXM><<<grd, blk, 0, g.st>>>(a);
     else if (E) rhs_global<false, true, AUXM><<<grd, blk, 0, g.st>>>(a);
     else rhs_global<false, false, AUXM><<<grd, blk, 0, g.st>>>(a);
+  } else if (M && !g.use_march1) {
+    // MHD: two threads per cell (momentum warps + induction warps)
+    a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
+    dim3 blk(TX, TY, 2), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
+    *nblocks_out = grd.x * grd.y * grd.z;
+    if (E) { if (g.zwin) rhs_march2<true, AUXM, true><<<grd, blk, March2Cfg<true, AUXM>::SMEM, g.st>>>(a);
+             else        rhs_march2<true, AUXM, false><<<grd, blk, March2Cfg<true, AUXM>::SMEM, g.st>>>(a); }
+    else   { if (g.zwin) rhs_march2<false, AUXM, true><<<grd, blk, March2Cfg<false, AUXM>::SMEM, g.st>>>(a);
+             else        rhs_march2<false, AUXM, false><<<grd, blk, March2Cfg<false, AUXM>::SMEM, g.st>>>(a); }
   } else {
     a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
     dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);

@@ -68,10 +68,57 @@ struct CellAux {
   double dtc, dtu, dtnu, dtchi;
 };
 
-// rhs[role] receives dX/dt for each present role.
+// what the induction part hands to the momentum/entropy part
+struct MagOut {
+  double fx, fy, fz;     // Lorentz force J x B / rho (magnetic.f90:4360)
+  double j2;             // for Ohmic heating (magnetic.f90:5127)
+  double advec_va2;      // Alfven CFL term (magnetic.f90:5438)
+  double b2, ab, jb;     // diagnostics
+};
+
+// ---------------- magnetic (magnetic.f90:3587-3990, 4229-5589) ----------------
+// rhsA[0..2] = dA/dt = u x B + eta del2 A (magnetic.f90:4399,5238,5521)
+template <bool AUX, class A>
+PC_DEV void mag_part(const A &a, const DevPar &c, double ux, double uy, double uz, double rho1,
+                     double *__restrict__ rhsA, MagOut &m)
+{
+  const double axy = ddy<R_AX>(a, c.fy1), axz = ddz<R_AX>(a, c.fz1);
+  const double ayx = ddx<R_AY>(a, c.fx1), ayz = ddz<R_AY>(a, c.fz1);
+  const double azx = ddx<R_AZ>(a, c.fx1), azy = ddy<R_AZ>(a, c.fy1);
+  const double bx = azy - ayz, by = axz - azx, bz = ayx - axy;   // curl_mn
+  // second derivatives (gij_etc, sub.f90:2732): del2 A and J = curl curl A / mu0
+  const double axxx = d2x<R_AX>(a, c.fx2), axyy = d2y<R_AX>(a, c.fy2), axzz = d2z<R_AX>(a, c.fz2);
+  const double ayxx = d2x<R_AY>(a, c.fx2), ayyy = d2y<R_AY>(a, c.fy2), ayzz = d2z<R_AY>(a, c.fz2);
+  const double azxx = d2x<R_AZ>(a, c.fx2), azyy = d2y<R_AZ>(a, c.fy2), azzz = d2z<R_AZ>(a, c.fz2);
+  // jj(1)=bij(3,2)-bij(2,3) etc. with bij(i,l)=eps d2A (sub.f90:2773-2781, magnetic.f90:3787)
+  const double jx = c.mu01 * ((dxy<R_AY>(a, c.fxy) - axyy) - (axzz - dxz<R_AZ>(a, c.fzx)));
+  const double jy = c.mu01 * ((dyz<R_AZ>(a, c.fyz) - ayzz) - (ayxx - dxy<R_AX>(a, c.fxy)));
+  const double jz = c.mu01 * ((dxz<R_AX>(a, c.fzx) - azxx) - (azyy - dyz<R_AY>(a, c.fyz)));
+  m.j2 = jx * jx + jy * jy + jz * jz;
+  m.fx = rho1 * (jy * bz - jz * by);
+  m.fy = rho1 * (jz * bx - jx * bz);
+  m.fz = rho1 * (jx * by - jy * bx);
+  rhsA[0] = (uy * bz - uz * by) + c.eta * (axxx + axyy + axzz);
+  rhsA[1] = (uz * bx - ux * bz) + c.eta * (ayxx + ayyy + ayzz);
+  rhsA[2] = (ux * by - uy * bx) + c.eta * (azxx + azyy + azzz);
+  if (AUX) {
+    const double t0 = bx * c.dx_1, t1 = by * c.dy_1, t2 = bz * c.dz_1;
+    m.advec_va2 = (t0 * t0 + t1 * t1 + t2 * t2) * c.mu01 * rho1;
+    m.b2 = bx * bx + by * by + bz * bz;
+    const double ax = a.template c<R_AX>(), ay = a.template c<R_AY>(), az = a.template c<R_AZ>();
+    m.ab = ax * bx + ay * by + az * bz;
+    m.jb = jx * bx + jy * by + jz * bz;
+  }
+}
+
+// ---------------- momentum, continuity, entropy + CFL ----------------
+// rhs[R_UX..R_UZ], rhs[R_LNRHO], rhs[R_SS]; m = output of mag_part (zeros without magnetic)
 // iz = z index of the cell relative to n1 (for the 1-D z profiles).
+// quantities the hydro part keeps until the induction part's results are in
+struct HydroPend { double ohm, advec_uu, advec_cs2, dt1_diffus, hm; };
+
 template <bool MAG, bool ENT, bool AUX, class A>
-PC_DEV void rhs_cell(const A &a, const DevPar &c, int iz, double *__restrict__ rhs, CellAux &aux)
+PC_DEV void hydro_pre(const A &a, const DevPar &c, int iz, double *__restrict__ rhs, CellAux &aux, HydroPend &p)
 {
   // ---------------- hydro pencils (hydro.f90:2913-3207) ----------------
   const double ux = a.template c<R_UX>(), uy = a.template c<R_UY>(), uz = a.template c<R_UZ>();
@@ -146,51 +193,15 @@ PC_DEV void rhs_cell(const A &a, const DevPar &c, int iz, double *__restrict__ r
   double duy = -uguy - c.Omega2 * ux + c.nu * (del2uy + 2.0 * sgly + third * gdy) + fpy;
   double duz = -uguz + c.nu * (del2uz + 2.0 * sglz + third * gdz) + fpz;
   if (c.lgravz) duz += c.gravz;                                    // gravity_simple.f90:914
+  rhs[R_UX] = dux; rhs[R_UY] = duy; rhs[R_UZ] = duz;
 
   // ---------------- continuity (density.f90:2542-2623) ----------------
   rhs[R_LNRHO] = -divu - uglnrho;
 
-  const double sij2 = sxx * sxx + syy * syy + szz * szz + 2.0 * (sxy * sxy + sxz * sxz + syz * syz);
-  double advec_va2 = 0.0, j2 = 0.0, b2 = 0.0, ab = 0.0, jb = 0.0;
-
-  // ---------------- magnetic (magnetic.f90:3587-3990, 4229-5589) ----------------
-  if (MAG) {
-    const double axy = ddy<R_AX>(a, c.fy1), axz = ddz<R_AX>(a, c.fz1);
-    const double ayx = ddx<R_AY>(a, c.fx1), ayz = ddz<R_AY>(a, c.fz1);
-    const double azx = ddx<R_AZ>(a, c.fx1), azy = ddy<R_AZ>(a, c.fy1);
-    const double bx = azy - ayz, by = axz - azx, bz = ayx - axy;   // curl_mn
-    b2 = bx * bx + by * by + bz * bz;
-    // second derivatives (gij_etc, sub.f90:2732): del2 A and J = curl curl A / mu0
-    const double axxx = d2x<R_AX>(a, c.fx2), axyy = d2y<R_AX>(a, c.fy2), axzz = d2z<R_AX>(a, c.fz2);
-    const double ayxx = d2x<R_AY>(a, c.fx2), ayyy = d2y<R_AY>(a, c.fy2), ayzz = d2z<R_AY>(a, c.fz2);
-    const double azxx = d2x<R_AZ>(a, c.fx2), azyy = d2y<R_AZ>(a, c.fy2), azzz = d2z<R_AZ>(a, c.fz2);
-    const double del2ax = axxx + axyy + axzz, del2ay = ayxx + ayyy + ayzz, del2az = azxx + azyy + azzz;
-    // jj(1)=bij(3,2)-bij(2,3) etc. with bij(i,l)=eps d2A (sub.f90:2773-2781, magnetic.f90:3787)
-    const double jx = c.mu01 * ((dxy<R_AY>(a, c.fxy) - axyy) - (axzz - dxz<R_AZ>(a, c.fzx)));
-    const double jy = c.mu01 * ((dyz<R_AZ>(a, c.fyz) - ayzz) - (ayxx - dxy<R_AX>(a, c.fxy)));
-    const double jz = c.mu01 * ((dxz<R_AX>(a, c.fzx) - azxx) - (azyy - dyz<R_AY>(a, c.fyz)));
-    j2 = jx * jx + jy * jy + jz * jz;
-    // Lorentz force J x B / rho (magnetic.f90:4360)
-    dux += rho1 * (jy * bz - jz * by);
-    duy += rho1 * (jz * bx - jx * bz);
-    duz += rho1 * (jx * by - jy * bx);
-    // induction: dA/dt = u x B + eta del2 A (magnetic.f90:4399,5238,5521)
-    rhs[R_AX] = (uy * bz - uz * by) + c.eta * del2ax;
-    rhs[R_AY] = (uz * bx - ux * bz) + c.eta * del2ay;
-    rhs[R_AZ] = (ux * by - uy * bx) + c.eta * del2az;
-    const double t0 = bx * c.dx_1, t1 = by * c.dy_1, t2 = bz * c.dz_1;
-    advec_va2 = (t0 * t0 + t1 * t1 + t2 * t2) * c.mu01 * rho1;    // magnetic.f90:5438
-    if (AUX) {
-      const double ax = a.template c<R_AX>(), ay = a.template c<R_AY>(), az = a.template c<R_AZ>();
-      ab = ax * bx + ay * by + az * bz;
-      jb = jx * bx + jy * by + jz * bz;
-    }
-  }
-  rhs[R_UX] = dux; rhs[R_UY] = duy; rhs[R_UZ] = duz;
-
   // ---------------- entropy equation (entropy.f90:3242-3452) ----------------
   double Hmax = 0.0, diffus_chi = 0.0;
   if (ENT) {
+    const double sij2 = sxx * sxx + syy * syy + szz * szz + 2.0 * (sxy * sxy + sxz * sxz + syz * syz);
     double dss = -ugss;
     const double visc_heat = 2.0 * c.nu * sij2;                    // viscosity.f90:1447
     if (c.lviscosity_heat) { dss += TT1 * visc_heat; Hmax += visc_heat; }
@@ -210,30 +221,59 @@ PC_DEV void rhs_cell(const A &a, const DevPar &c, int iz, double *__restrict__ r
       dss += TT1 * rho1 * heat;
       Hmax += heat * rho1;
     }
-    if (MAG && c.lohmic_heat) dss += c.eta * c.mu0 * j2 * rho1 * TT1;   // magnetic.f90:5127
+    p.ohm = (MAG && c.lohmic_heat) ? c.eta * c.mu0 * rho1 * TT1 : 0.0;   // magnetic.f90:5127
     rhs[R_SS] = dss;
   }
 
-  // ---------------- time-step constraint (equ.f90:1086-1151) ----------------
+  // ---------------- time-step constraint, part 1 (equ.f90:1086-1151) ----------------
   if (AUX) {
-    const double advec_uu = aux_ * c.dx_1 + auy_ * c.dy_1 + auz_ * c.dz_1;      // hydro.f90:3810
-    const double advec_cs2 = cs2 * c.dxyz_2;
-    const double maxadvec = advec_uu + sqrt(advec_va2 + advec_cs2);
+    p.advec_uu = aux_ * c.dx_1 + auy_ * c.dy_1 + auz_ * c.dz_1;                  // hydro.f90:3810
+    p.advec_cs2 = cs2 * c.dxyz_2;
     double maxdiffus = c.nu * c.dxyz_2;
     if (MAG) maxdiffus = fmax(maxdiffus, c.eta * c.dxyz_2);
     if (ENT) maxdiffus = fmax(maxdiffus, diffus_chi);
-    const double dt1_advec = maxadvec / c.cdt, dt1_diffus = maxdiffus / c.cdtv;
-    double dt1 = sqrt(dt1_advec * dt1_advec + dt1_diffus * dt1_diffus);
-    if (ENT) dt1 = fmax(dt1, fabs(Hmax / ee / c.cdts));                          // entropy.f90:3444
-    aux.dt1 = dt1;
+    p.dt1_diffus = maxdiffus / c.cdtv;
+    p.hm = ENT ? fabs(Hmax / ee / c.cdts) : 0.0;                                 // entropy.f90:3444
     aux.u2 = ux * ux + uy * uy + uz * uz;
     aux.rho = 1.0 / rho1;
     aux.ss = ss;
-    aux.b2 = b2; aux.j2 = j2; aux.ab = ab; aux.jb = jb;
     aux.ou = (uzy - uyz) * ux + (uxz - uzx) * uy + (uyx - uxy) * uz;
-    aux.dtc = sqrt(advec_cs2) / c.cdt;
-    aux.dtu = advec_uu / c.cdt;
+    aux.dtc = sqrt(p.advec_cs2) / c.cdt;
+    aux.dtu = p.advec_uu / c.cdt;
     aux.dtnu = c.nu * c.dxyz_2 / c.cdtv;
     aux.dtchi = diffus_chi / c.cdtv;
   }
+}
+
+// adds what depends on the induction part: Lorentz force, Ohmic heating, Alfven CFL term
+template <bool MAG, bool ENT, bool AUX>
+PC_DEV void hydro_finish(const DevPar &c, const HydroPend &p, const MagOut &m, double *__restrict__ rhs, CellAux &aux)
+{
+  if (MAG) {
+    rhs[R_UX] += m.fx; rhs[R_UY] += m.fy; rhs[R_UZ] += m.fz;
+    if (ENT) rhs[R_SS] += p.ohm * m.j2;
+  }
+  if (AUX) {
+    const double maxadvec = p.advec_uu + sqrt((MAG ? m.advec_va2 : 0.0) + p.advec_cs2);
+    const double dt1_advec = maxadvec / c.cdt;
+    double dt1 = sqrt(dt1_advec * dt1_advec + p.dt1_diffus * p.dt1_diffus);
+    if (ENT) dt1 = fmax(dt1, p.hm);
+    aux.dt1 = dt1;
+    aux.b2 = MAG ? m.b2 : 0.0; aux.j2 = MAG ? m.j2 : 0.0; aux.ab = MAG ? m.ab : 0.0; aux.jb = MAG ? m.jb : 0.0;
+  }
+}
+
+// one thread does both parts (global-memory kernel, non-specialised marching kernel)
+template <bool MAG, bool ENT, bool AUX, class A>
+PC_DEV void rhs_cell(const A &a, const DevPar &c, int iz, double *__restrict__ rhs, CellAux &aux)
+{
+  MagOut m;
+  m.fx = m.fy = m.fz = m.j2 = m.advec_va2 = m.b2 = m.ab = m.jb = 0.0;
+  if (MAG) {
+    const double rho1 = exp(-a.template c<R_LNRHO>());
+    mag_part<AUX>(a, c, a.template c<R_UX>(), a.template c<R_UY>(), a.template c<R_UZ>(), rho1, rhs + R_AX, m);
+  }
+  HydroPend p;
+  hydro_pre<MAG, ENT, AUX>(a, c, iz, rhs, aux, p);
+  hydro_finish<MAG, ENT, AUX>(c, p, m, rhs, aux);
 }
