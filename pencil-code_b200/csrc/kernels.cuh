@@ -478,253 +478,211 @@ __global__ void bc_fill(BcArgs b)
   }
 }
 
-// ------------------------------------------------------------------------
-// Warp-specialised z-marching kernel for MHD (rhs_march2).
-//
-// The plane ring pins one CTA per SM (about 830 B of shared memory per tile
-// cell), so occupancy can only grow by putting TWO threads on each cell:
-// threadIdx.z==0 ("hydro" warps) evaluates momentum/continuity/entropy,
-// threadIdx.z==1 ("mag" warps) the induction equation and J x B.  Each role
-// keeps only its own z-column window in registers (<=128 registers/thread,
-// 16 warps/SM instead of 8).  The mag role hands J x B/rho (+ j^2, Alfven CFL
-// term) to the hydro role through shared memory; a named barrier protects
-// the single exchange buffer.
-// ------------------------------------------------------------------------
-#define NTHR2 (2 * NTHR)
 
-template <bool ZWIN>
-struct MarchAcc2 {
-  const double *smem0;    // start of dynamic shared memory (ring at 0, plain fields behind it)
-  unsigned sb[7];         // byte offset of this thread's cell in the ring slot of plane z+k (k=-3..3)
-  unsigned pb;            // byte offset of this thread's cell in the plain-field slot of plane z
-  double w[NROLE][7];     // own column, planes z-3..z+3 (ring roles only when ZWIN)
+// ------------------------------------------------------------------------
+// rhs_tma: the production z-marching kernel.  Same scheme as rhs_march, but
+//  * plane tiles are fetched by the TMA unit (cp.async.bulk.tensor.3d, one
+//    box {HX,HY,1} per field and plane, completion on an mbarrier) instead of
+//    8-byte cp.async issued by every thread: frees the LSU queue (no
+//    lg_throttle), zero-fills out-of-range halo at the domain edge;
+//  * whether the 2N register w is read is a template parameter (RW), so its
+//    prefetch is an unconditional load that the compiler can keep in flight;
+//  * edge tiles clamp their column instead of predicating the whole body.
+// The global tensor is f viewed as 3-D (mx, my, mz*mvar).
+// ------------------------------------------------------------------------
+#include <cuda.h>
+
+#define PEP 544                 // plane tile padded to a multiple of 128 B (TMA smem alignment)
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{ asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count)); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{ asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra.uni WAIT_DONE;\n"
+      "bra.uni WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, int x, int y, int z, unsigned long long *bar)
+{
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+               ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar)) : "memory");
+}
+
+template <bool MAG, bool ENT>
+struct TmaAcc {
+  const double *smem0;  // ring [ring role][NSLOT][PEP], then plain [plain role][2][PEP]
+  unsigned sb[7];       // byte offset of this thread's cell in the ring slot of plane z+k, k=-3..3
+  unsigned pb;          // byte offset of this thread's cell in the plain-field slot of plane z
+  double w[NROLE][7];   // own column, planes z-3..z+3
   template <int R, int OFF> PC_DEV double cenv() const
-  { return R < 6 ? lds_at(smem0, sb[3], (R * NSLOT) * PE + OFF) : lds_at(smem0, pb, ((R - 6) * 2) * PE + OFF); }
-  template <int R> PC_DEV double c() const { return (R < 6 && !ZWIN) ? cenv<R, 0>() : w[R][3]; }
+  { return R < 6 ? lds_at(smem0, sb[3], (R * NSLOT) * PEP + OFF) : lds_at(smem0, pb, ((R - 6) * 2) * PEP + OFF); }
+  template <int R> PC_DEV double c() const { return w[R][3]; }
   template <int R, int K> PC_DEV double x() const { return cenv<R, K>(); }
   template <int R, int K> PC_DEV double y() const { return cenv<R, K * HX>(); }
-  template <int R, int K> PC_DEV double z() const { return (R < 6 && !ZWIN) ? lds_at(smem0, sb[3 + K], (R * NSLOT) * PE) : w[R][3 + K]; }
+  template <int R, int K> PC_DEV double z() const { return w[R][3 + K]; }
   template <int R, int KX, int KY> PC_DEV double xy() const { return cenv<R, KX + KY * HX>(); }
-  template <int R, int KX, int KZ> PC_DEV double xz() const { return lds_at(smem0, sb[3 + KZ], (R * NSLOT) * PE + KX); }
-  template <int R, int KY, int KZ> PC_DEV double yz() const { return lds_at(smem0, sb[3 + KZ], (R * NSLOT) * PE + KY * HX); }
+  template <int R, int KX, int KZ> PC_DEV double xz() const { return lds_at(smem0, sb[3 + KZ], (R * NSLOT) * PEP + KX); }
+  template <int R, int KY, int KZ> PC_DEV double yz() const { return lds_at(smem0, sb[3 + KZ], (R * NSLOT) * PEP + KY * HX); }
 };
 
-template <bool ENT, int AUXM> struct March2Cfg {
+template <bool MAG, bool ENT> struct TmaCfg {
+  static constexpr int NRF = MAG ? 6 : 3;
   static constexpr int NPF = ENT ? 2 : 1;
-  static constexpr int NEX = 3 + (ENT ? 1 : 0) + (AUXM > 0 ? 1 : 0);
-  static constexpr size_t EXB = (size_t)NEX * NTHR > (size_t)16 * NRED ? (size_t)NEX * NTHR : (size_t)16 * NRED;
-  static constexpr size_t SMEM = sizeof(double) * ((size_t)6 * NSLOT * PE + (size_t)NPF * 2 * PE + EXB);
+  static constexpr int NDBL = NRF * NSLOT * PEP + NPF * 2 * PEP;          // field tiles
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + 8 * NRED + 2) + 128;   // + reduction scratch + mbarrier + alignment slack
 };
 
-template <bool ENT, int AUXM, bool ZWIN>
-__global__ void __launch_bounds__(NTHR2, 1) rhs_march2(SubstepArgs a)
+template <bool MAG, bool ENT, int AUXM, bool RW>
+__global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_constant__ CUtensorMap tmap)
 {
   const DevPar &c = c_par;
-  extern __shared__ double smem[];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  // align the tile area to 128 B (TMA destination requirement)
+  double *smem = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  constexpr int NRF = TmaCfg<MAG, ENT>::NRF, NPF = TmaCfg<MAG, ENT>::NPF;
   double *ring = smem;
-  double *plain = smem + (size_t)6 * NSLOT * PE;
-  double *exch = plain + (size_t)March2Cfg<ENT, AUXM>::NPF * 2 * PE;
-  constexpr int NEX = March2Cfg<ENT, AUXM>::NEX;
+  double *plain = smem + (size_t)NRF * NSLOT * PEP;
+  double *redsm = plain + (size_t)NPF * 2 * PEP;
+  unsigned long long *bar = reinterpret_cast<unsigned long long *>(redsm + 8 * NRED);
+  constexpr unsigned BOX_BYTES = PE * 8;
 
-  const int tx = threadIdx.x, ty = threadIdx.y, role = threadIdx.z;
-  const int tid = ty * TX + tx;                 // cell index in the tile
-  const int tid2 = tid + role * NTHR;           // thread index in the CTA
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx;
   const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
   const int zb = a.z_lo + blockIdx.z * a.zchunk;
   const int ze = min(zb + a.zchunk, a.z_hi);
   const bool active = (x0 + tx < c.nx) && (y0 + ty < c.ny);
-
-  // share of a plane tile per thread: elements tid2 and tid2+512
-  int eoff[2]; long long goff[2]; bool eok[2];
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    const int e = tid2 + i * NTHR2;
-    const int hy = e / HX, hx = e - hy * HX;
-    eoff[i] = e;
-    eok[i] = e < PE && (x0 + hx) < c.mx && (y0 + hy) < c.my;
-    goff[i] = (long long)(y0 + hy) * c.sy + (x0 + hx);
-  }
-  const long long col = (long long)(y0 + ty + NG) * c.sy + (x0 + tx + NG);
+  // edge tiles: inactive threads shadow the last valid cell (loads stay in range, stores are masked)
+  const int lx = min(x0 + tx, c.nx - 1), ly = min(y0 + ty, c.ny - 1);
+  const long long col = (long long)(ly + NG) * c.sy + (lx + NG);
   const int tb = (ty + NG) * HX + tx + NG;
+  const bool ww = a.write_w != 0 && active, wf = a.write_f != 0 && active;
 
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
   // prologue: ring planes zb..zb+6 (padded) -> slots 0..6, plain plane zb+NG -> slot 0
+  if (tid == 0) {
+    mbar_expect_tx(bar, (unsigned)((NRF * 7 + NPF) * BOX_BYTES));
 #pragma unroll 1
-  for (int q = 0; q < 7; q++) {
-    const long long pz = (long long)(zb + q) * c.sz;
+    for (int q = 0; q < 7; q++)
 #pragma unroll
-    for (int r = 0; r < 6; r++) {
-      const double *src = a.f_in + c.foff[r] + pz;
+      for (int r = 0; r < 6; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        tma_load_3d(ring + ((size_t)r * NSLOT + q) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + q, bar);
+      }
 #pragma unroll
-      for (int i = 0; i < 2; i++) if (eok[i]) cp_async8(ring + ((size_t)r * NSLOT + q) * PE + eoff[i], src + goff[i]);
+    for (int r = 6; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+      tma_load_3d(plain + ((size_t)(r - 6) * 2) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + NG, bar);
     }
   }
-#pragma unroll
-  for (int r = 6; r < NROLE; r++) {
-    if (r == R_SS && !ENT) continue;
-    const double *src = a.f_in + c.foff[r] + (long long)(zb + NG) * c.sz;
-#pragma unroll
-    for (int i = 0; i < 2; i++) if (eok[i]) cp_async8(plain + ((size_t)(r - 6) * 2) * PE + eoff[i], src + goff[i]);
-  }
-  cp_async_commit();
-
-  MarchAcc2<ZWIN> acc;
+  TmaAcc<MAG, ENT> acc;
   acc.smem0 = smem;
   double wnext[NROLE];
-  if (role == 0) {
 #pragma unroll
-    for (int r = 0; r < NROLE; r++) {
-      const bool mine = (r <= R_UZ && ZWIN) || r == R_LNRHO || (r == R_SS && ENT);
-      if (!mine) continue;
+  for (int r = 0; r < NROLE; r++) {
+    if (!role_present<MAG, ENT>(r)) continue;
+    const double *src = a.f_in + c.foff[r] + col;
 #pragma unroll
-      for (int k = 0; k < 7; k++) acc.w[r][k] = active ? __ldg(a.f_in + c.foff[r] + col + (long long)(zb + k) * c.sz) : 0.0;
-    }
-  } else if (ZWIN) {
-#pragma unroll
-    for (int r = R_AX; r <= R_AZ; r++)
-#pragma unroll
-      for (int k = 0; k < 7; k++) acc.w[r][k] = active ? __ldg(a.f_in + c.foff[r] + col + (long long)(zb + k) * c.sz) : 0.0;
+    for (int k = 0; k < 7; k++) acc.w[r][k] = __ldg(src + (long long)(zb + k) * c.sz);
   }
   double red[NRED];
 #pragma unroll
   for (int q = 0; q < NRED; q++) red[q] = 0.0;
   const double beta_dt = a.write_f ? a.beta * a.dt_dev[0] : 0.0;
-  if (role == 0) asm volatile("bar.arrive 1, %0;" ::"n"(NTHR2));   // exchange buffer starts out free
-  cp_async_wait_all();
-  __syncthreads();
+  unsigned phase = 0;
+  mbar_wait(bar, phase);
+  phase ^= 1;
 
 #pragma unroll 1
   for (int n = zb; n < ze; n++) {
     const int q0 = n - zb;
     const bool more = n + 1 < ze;
-    // 1. stage the next planes
+    // 1. the TMA unit stages the next planes (ring: padded plane n+7, plain: padded plane n+NG+1)
     if (more) {
-      const int sl = (q0 + 7) & (NSLOT - 1);
-      const long long pz = (long long)(n + 7) * c.sz;
+      if (tid == 0) {
+        mbar_expect_tx(bar, (unsigned)((NRF + NPF) * BOX_BYTES));
+        const int sl = (q0 + 7) & (NSLOT - 1);
 #pragma unroll
-      for (int r = 0; r < 6; r++) {
-        const double *src = a.f_in + c.foff[r] + pz;
+        for (int r = 0; r < 6; r++) {
+          if (!role_present<MAG, ENT>(r)) continue;
+          tma_load_3d(ring + ((size_t)r * NSLOT + sl) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + n + 7, bar);
+        }
+        const int ps = (q0 + 1) & 1;
 #pragma unroll
-        for (int i = 0; i < 2; i++) if (eok[i]) cp_async8(ring + ((size_t)r * NSLOT + sl) * PE + eoff[i], src + goff[i]);
+        for (int r = 6; r < NROLE; r++) {
+          if (!role_present<MAG, ENT>(r)) continue;
+          tma_load_3d(plain + ((size_t)(r - 6) * 2 + ps) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + n + NG + 1, bar);
+        }
       }
-      const int ps = (q0 + 1) & 1;
-      const long long pz1 = (long long)(n + NG + 1) * c.sz;
 #pragma unroll
       for (int r = 6; r < NROLE; r++) {
-        if (r == R_SS && !ENT) continue;
-        const double *src = a.f_in + c.foff[r] + pz1;
-#pragma unroll
-        for (int i = 0; i < 2; i++) if (eok[i]) cp_async8(plain + ((size_t)(r - 6) * 2 + ps) * PE + eoff[i], src + goff[i]);
+        if (!role_present<MAG, ENT>(r)) continue;
+        wnext[r] = __ldg(a.f_in + c.foff[r] + col + (long long)(n + 7) * c.sz);
       }
-      cp_async_commit();
     }
-#pragma unroll
-    for (int k = 0; k < 7; k++) acc.sb[k] = (unsigned)((((q0 + k) & (NSLOT - 1)) * PE + tb) * 8);
-    acc.pb = (unsigned)((6 * NSLOT * PE + (q0 & 1) * PE + tb) * 8);
     const long long idx = (long long)(n + NG) * c.sz + col;
-
-    if (role == 1) {
-      // ===================== induction warps =====================
-      double wold[3], rhsA[3];
-      MagOut m;
-      if (active) {
+    // old 2N register: unconditional loads, consumed only after the stencils
+    double wold[NROLE];
+    if (RW) {
 #pragma unroll
-        for (int j = 0; j < 3; j++) wold[j] = a.alpha != 0.0 ? __ldcs(a.w + idx + c.foff[R_AX + j]) : 0.0;
-        const double ux = acc.template cenv<R_UX, 0>(), uy = acc.template cenv<R_UY, 0>(), uz = acc.template cenv<R_UZ, 0>();
-        const double rho1 = exp(-acc.template cenv<R_LNRHO, 0>());
-        mag_part<(AUXM > 0)>(acc, c, ux, uy, uz, rho1, rhsA, m);
-#pragma unroll
-        for (int j = 0; j < 3; j++) {
-          const double wv = rhsA[j] + a.alpha * wold[j];
-          const double f0 = j == 0 ? acc.template c<R_AX>() : (j == 1 ? acc.template c<R_AY>() : acc.template c<R_AZ>());
-          if (a.write_w) __stcs(a.w + idx + c.foff[R_AX + j], wv);
-          if (a.write_f) __stcs(a.f_out + idx + c.foff[R_AX + j], f0 + beta_dt * wv);
-        }
-        if (AUXM > 1) {
-          red[RD_B2MAX] = fmax(red[RD_B2MAX], m.b2); red[RD_J2MAX] = fmax(red[RD_J2MAX], m.j2);
-          red[RS_B2] += m.b2; red[RS_J2] += m.j2; red[RS_AB] += m.ab; red[RS_JB] += m.jb;
-        }
-      }
-      asm volatile("bar.sync 1, %0;" ::"n"(NTHR2) : "memory");        // hydro warps have consumed the previous hand-over
-      if (active) {
-        exch[0 * NTHR + tid] = m.fx; exch[1 * NTHR + tid] = m.fy; exch[2 * NTHR + tid] = m.fz;
-        if (ENT) exch[3 * NTHR + tid] = m.j2;
-        if (AUXM > 0) exch[(NEX - 1) * NTHR + tid] = m.advec_va2;
+      for (int r = 0; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        wold[r] = __ldcs(a.w + idx + c.foff[r]);
       }
     }
-    double rhs[NROLE], wold[NROLE];
+    // 2. the cell of plane n
+#pragma unroll
+    for (int k = 0; k < 7; k++) acc.sb[k] = (unsigned)((((q0 + k) & (NSLOT - 1)) * PEP + tb) * 8);
+    acc.pb = (unsigned)((NRF * NSLOT * PEP + (q0 & 1) * PEP + tb) * 8);
+    double rhs[NROLE];
     CellAux aux;
-    HydroPend pend;
-    if (role == 0 && active) {
-      // ===================== momentum / continuity / entropy warps =====================
+    rhs_cell<MAG, ENT, (AUXM > 0)>(acc, c, n, rhs, aux);
+    // 3. 2N-RK3 update (timestep.f90:119-122,162-163); f_in(cell) is the window centre
 #pragma unroll
-      for (int r = 0; r < NROLE; r++) {
-        if ((r >= R_AX && r <= R_AZ) || (r == R_SS && !ENT)) continue;
-        wold[r] = a.alpha != 0.0 ? __ldcs(a.w + idx + c.foff[r]) : 0.0;
-      }
-      if (more) {
-        wnext[R_LNRHO] = __ldg(a.f_in + c.foff[R_LNRHO] + col + (long long)(n + 7) * c.sz);
-        if (ENT) wnext[R_SS] = __ldg(a.f_in + c.foff[R_SS] + col + (long long)(n + 7) * c.sz);
-      }
-      // everything that does not need J and B; the rest follows after the hand-over
-      hydro_pre<true, ENT, (AUXM > 0)>(acc, c, n, rhs, aux, pend);
+    for (int r = 0; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+      const long long i = idx + c.foff[r];
+      const double wv = RW ? rhs[r] + a.alpha * wold[r] : rhs[r];
+      if (ww) __stcs(a.w + i, wv);
+      if (wf) __stcs(a.f_out + i, acc.w[r][3] + beta_dt * wv);
     }
-    // 2. hand-over point: next planes have landed, every warp is done reading the oldest plane
-    cp_async_wait_all();
+    if (AUXM > 0 && active) {
+      red[RD_DT1] = fmax(red[RD_DT1], aux.dt1);
+      if (AUXM > 1) {
+        red[RD_U2MAX] = fmax(red[RD_U2MAX], aux.u2); red[RD_B2MAX] = fmax(red[RD_B2MAX], aux.b2);
+        red[RD_J2MAX] = fmax(red[RD_J2MAX], aux.j2);
+        red[RD_DTC] = fmax(red[RD_DTC], aux.dtc); red[RD_DTU] = fmax(red[RD_DTU], aux.dtu);
+        red[RD_DTNU] = fmax(red[RD_DTNU], aux.dtnu); red[RD_DTCHI] = fmax(red[RD_DTCHI], aux.dtchi);
+        red[RS_U2] += aux.u2; red[RS_RHO] += aux.rho; red[RS_SS] += aux.ss; red[RS_B2] += aux.b2; red[RS_J2] += aux.j2;
+        red[RS_AB] += aux.ab; red[RS_JB] += aux.jb; red[RS_OU] += aux.ou;
+      }
+    }
+    // 4. next planes have landed; everybody is done with the oldest plane
+    if (more) { mbar_wait(bar, phase); phase ^= 1; }
     __syncthreads();
-    if (role == 0) {
-      if (active) {
-        MagOut m;
-        m.fx = exch[0 * NTHR + tid]; m.fy = exch[1 * NTHR + tid]; m.fz = exch[2 * NTHR + tid];
-        m.j2 = ENT ? exch[3 * NTHR + tid] : 0.0;
-        m.advec_va2 = AUXM > 0 ? exch[(NEX - 1) * NTHR + tid] : 0.0;
-        m.b2 = m.ab = m.jb = 0.0;                       // accumulated by the mag warps themselves
-        hydro_finish<true, ENT, (AUXM > 0)>(c, pend, m, rhs, aux);
-        if (AUXM > 0) {
-          red[RD_DT1] = fmax(red[RD_DT1], aux.dt1);
-          if (AUXM > 1) {
-            red[RD_U2MAX] = fmax(red[RD_U2MAX], aux.u2);
-            red[RD_DTC] = fmax(red[RD_DTC], aux.dtc); red[RD_DTU] = fmax(red[RD_DTU], aux.dtu);
-            red[RD_DTNU] = fmax(red[RD_DTNU], aux.dtnu); red[RD_DTCHI] = fmax(red[RD_DTCHI], aux.dtchi);
-            red[RS_U2] += aux.u2; red[RS_RHO] += aux.rho; red[RS_SS] += aux.ss; red[RS_OU] += aux.ou;
-          }
-        }
-      }
-      if (more) asm volatile("bar.arrive 1, %0;" ::"n"(NTHR2) : "memory");
-    }
-    if (role == 0 && active) {
 #pragma unroll
-      for (int r = 0; r < NROLE; r++) {
-        if ((r >= R_AX && r <= R_AZ) || (r == R_SS && !ENT)) continue;
-        const double wv = rhs[r] + a.alpha * wold[r];
-        const double f0 = r == R_UX ? acc.template c<R_UX>() : r == R_UY ? acc.template c<R_UY>() : r == R_UZ ? acc.template c<R_UZ>()
-                        : r == R_LNRHO ? acc.template c<R_LNRHO>() : acc.template c<R_SS>();
-        if (a.write_w) __stcs(a.w + idx + c.foff[r], wv);
-        if (a.write_f) __stcs(a.f_out + idx + c.foff[r], f0 + beta_dt * wv);
-      }
-    }
-    // 3. slide the z windows
-    if (role == 0) {
+    for (int r = 0; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
 #pragma unroll
-      for (int r = 0; r < NROLE; r++) {
-        const bool mine = (r <= R_UZ && ZWIN) || r == R_LNRHO || (r == R_SS && ENT);
-        if (!mine) continue;
-#pragma unroll
-        for (int k = 0; k < 6; k++) acc.w[r][k] = acc.w[r][k + 1];
-        if (r <= R_UZ) acc.w[r][6] = ring[((size_t)r * NSLOT + ((q0 + 7) & (NSLOT - 1))) * PE + tb];
-        else acc.w[r][6] = wnext[r];
-      }
-    } else if (ZWIN) {
-#pragma unroll
-      for (int r = R_AX; r <= R_AZ; r++) {
-#pragma unroll
-        for (int k = 0; k < 6; k++) acc.w[r][k] = acc.w[r][k + 1];
-        acc.w[r][6] = ring[((size_t)r * NSLOT + ((q0 + 7) & (NSLOT - 1))) * PE + tb];
-      }
+      for (int k = 0; k < 6; k++) acc.w[r][k] = acc.w[r][k + 1];
+      if (r < 6) acc.w[r][6] = ring[((size_t)r * NSLOT + ((q0 + 7) & (NSLOT - 1))) * PEP + tb];
+      else acc.w[r][6] = wnext[r];
     }
   }
   if (AUXM > 0) {
-    __syncthreads();      // exch is reused as reduction scratch
     const int bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-    block_reduce_store<AUXM>(red, tid2, NTHR2, exch, a.partials, bl);
+    block_reduce_store<AUXM>(red, tid, NTHR, redsm, a.partials, bl);
   }
 }

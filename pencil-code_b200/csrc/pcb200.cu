@@ -45,6 +45,8 @@ struct Ctx {
   DevPar hp;
   size_t nelem = 0;             // mw*mvar
   double *f[2] = {nullptr, nullptr}, *w = nullptr;
+  CUtensorMap tmap[2];          // TMA view of f[0], f[1] as (mx, my, mz*mvar)
+  bool have_tma = false;
   int cur = 0;
   double *partials = nullptr; size_t npartials = 0;
   double *red_dev = nullptr;    // [NRED]
@@ -56,8 +58,7 @@ struct Ctx {
   double dt = 0.0;
   double diag[PCB200_NDIAG];
   bool use_global = false;      // PCB200_KERNEL=global
-  bool use_march1 = false;      // PCB200_KERNEL=march1 (non-specialised marching kernel also for MHD)
-  bool zwin = true;             // PCB200_ZWIN=0: z neighbours of ring fields from shared memory
+  bool use_cpasync = false;     // PCB200_KERNEL=cpasync: cp.async staging instead of TMA
   int zchunk = 0;
   int64_t launches = 0;
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
@@ -97,9 +98,7 @@ extern "C" int pcb200_init(int local_rank)
     CK(cudaMallocHost(&g.pinned, sizeof(double) * (NRED + 2)));
     const char *k = getenv("PCB200_KERNEL");
     g.use_global = k && !strcmp(k, "global");
-    g.use_march1 = k && !strcmp(k, "march1");
-    const char *zw = getenv("PCB200_ZWIN");
-    if (zw) g.zwin = atoi(zw) != 0;
+    g.use_cpasync = k && !strcmp(k, "cpasync");
     const char *t = getenv("PCB200_TIME_RHS");
     g.time_rhs = t && atoi(t) != 0;
     g.inited = true;
@@ -112,6 +111,35 @@ static void free_fields()
   for (int i = 0; i < 2; i++) { if (g.f[i]) cudaFree(g.f[i]); g.f[i] = nullptr; }
   if (g.w) cudaFree(g.w); g.w = nullptr;
   if (g.partials) cudaFree(g.partials); g.partials = nullptr; g.npartials = 0;
+}
+
+// TMA descriptors: f seen as a 3-D tensor (mx, my, mz*mvar) of doubles, box {HX,HY,1}.
+// cuTensorMapEncodeTiled is taken from the driver at run time (no -lcuda).
+static int make_tensor_maps()
+{
+  g.have_tma = false;
+  const DevPar &h = g.hp;
+  if ((h.mx * 8) % 16 != 0) return PCB200_OK;          // global strides must be multiples of 16 B: cp.async path instead
+  typedef CUresult (*encode_t)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                               const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  void *fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || !fn || qres != cudaDriverEntryPointSuccess) { cudaGetLastError(); return PCB200_OK; }
+  encode_t encode = (encode_t)fn;
+  for (int i = 0; i < 2; i++) {
+    cuuint64_t dims[3] = {(cuuint64_t)h.mx, (cuuint64_t)h.my, (cuuint64_t)h.mz * h.mvar};
+    cuuint64_t strides[2] = {(cuuint64_t)h.mx * 8, (cuuint64_t)h.sz * 8};
+    cuuint32_t box[3] = {HX, HY, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = encode(&g.tmap[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, g.f[i], dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(PCB200_ECUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  }
+  g.have_tma = true;
+  return PCB200_OK;
 }
 
 extern "C" int pcb200_initialize(const pcb200_params *par)
@@ -170,6 +198,10 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
     g.cur = 0;
   }
   for (int q = 0; q < PCB200_NPROF; q++) h.zprof[q] = g.zprof[q];
+  {
+    int rc = make_tensor_maps();
+    if (rc) return rc;
+  }
   // z chunking: enough CTAs to fill 148 SMs a few times over, chunks >= 32 planes
   {
     const int tiles = ((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY);
@@ -193,12 +225,11 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   OPTIN(false, true, 0);  OPTIN(false, true, 1);  OPTIN(false, true, 2);
   OPTIN(true, true, 0);   OPTIN(true, true, 1);   OPTIN(true, true, 2);
 #undef OPTIN
-#define OPTIN2(E, A, Z) CK(cudaFuncSetAttribute(rhs_march2<E, A, Z>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)March2Cfg<E, A>::SMEM))
-  OPTIN2(false, 0, true); OPTIN2(false, 1, true); OPTIN2(false, 2, true);
-  OPTIN2(true, 0, true);  OPTIN2(true, 1, true);  OPTIN2(true, 2, true);
-  OPTIN2(false, 0, false); OPTIN2(false, 1, false); OPTIN2(false, 2, false);
-  OPTIN2(true, 0, false);  OPTIN2(true, 1, false);  OPTIN2(true, 2, false);
-#undef OPTIN2
+#define OPTINT(M, E, A, R) CK(cudaFuncSetAttribute(rhs_tma<M, E, A, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TmaCfg<M, E>::SMEM))
+#define OPTINT4(M, E) OPTINT(M, E, 0, false); OPTINT(M, E, 1, false); OPTINT(M, E, 2, false); OPTINT(M, E, 0, true)
+  OPTINT4(false, false); OPTINT4(true, false); OPTINT4(false, true); OPTINT4(true, true);
+#undef OPTINT4
+#undef OPTINT
   CK(cudaStreamSynchronize(g.st));
   g.have_par = true;
   return PCB200_OK;
@@ -338,15 +369,17 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     else if (M) rhs_global<true, false, AUXM><<<grd, blk, 0, g.st>>>(a);
     else if (E) rhs_global<false, true, AUXM><<<grd, blk, 0, g.st>>>(a);
     else rhs_global<false, false, AUXM><<<grd, blk, 0, g.st>>>(a);
-  } else if (M && !g.use_march1) {
-    // MHD: two threads per cell (momentum warps + induction warps)
+  } else if (g.have_tma && !g.use_cpasync) {
     a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
-    dim3 blk(TX, TY, 2), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
+    dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
     *nblocks_out = grd.x * grd.y * grd.z;
-    if (E) { if (g.zwin) rhs_march2<true, AUXM, true><<<grd, blk, March2Cfg<true, AUXM>::SMEM, g.st>>>(a);
-             else        rhs_march2<true, AUXM, false><<<grd, blk, March2Cfg<true, AUXM>::SMEM, g.st>>>(a); }
-    else   { if (g.zwin) rhs_march2<false, AUXM, true><<<grd, blk, March2Cfg<false, AUXM>::SMEM, g.st>>>(a);
-             else        rhs_march2<false, AUXM, false><<<grd, blk, March2Cfg<false, AUXM>::SMEM, g.st>>>(a); }
+    const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
+    const bool rw = a.alpha != 0.0;
+    // the old 2N register is only read on substeps 2,3, which never need the reductions
+#define LT(M, E) do { if (rw) rhs_tma<M, E, 0, true><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); \
+                      else    rhs_tma<M, E, AUXM, false><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); } while (0)
+    if (M && E) LT(true, true); else if (M) LT(true, false); else if (E) LT(false, true); else LT(false, false);
+#undef LT
   } else {
     a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
     dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
