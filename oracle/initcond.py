@@ -1,0 +1,110 @@
+"""Initial condition of samples/conv-slab, restated from the reference's start.x
+modules (TEST INFRASTRUCTURE: used to pin the oracle against the reference's own
+golden time series samples/conv-slab/reference.out.double).
+
+  lnrho: 'piecew-poly'  density.f90:1315-1345 + polytropic_lnrho_z (density.f90, same file)
+  ss   : 'piecew-poly'  entropy.f90:1628-1650 + polytropic_ss_z (entropy.f90:1849-1925)
+  uu   : 'up-down'      hydro.f90:2189-2203
+Parameters: samples/conv-slab/start.in.
+"""
+import math
+
+import numpy as np
+
+EPSI = 5 * np.finfo(np.float64).eps      # cparam.f90:118
+TINI = 5 * np.finfo(np.float64).tiny
+
+
+def _step(x, x0, width):                 # sub.f90:4544 step_vector
+    return 0.5 * (1 + np.tanh((x - x0) / (width + TINI)))
+
+
+def convslab_initial_condition(P, grid, *, cs0=0.57735, gamma=1.6666666, rho0=1.0, gravz=-1.0, z1=0.0, z2=1.0,
+                               zref=1.32, mpoly0=1.0, mpoly1=3.0, mpoly2=0.0, isothtop=1, widthlnrho=0.05,
+                               widthss=0.05, ampluu=0.1, widthuu=0.1, fac_cs=1.0, isothmid=0):
+    x, y, z = grid["x"], grid["y"], grid["zglobal"] if "zglobal" in grid and P.nprocz == 1 else grid["z"]
+    mx, my, mz = x.size, y.size, z.size
+    x0, y0, z0 = P.xyz0[0], P.xyz0[1], P.xyz0[2]
+    Lx, Ly, Lz = P.Lxyz[0], P.Lxyz[1], P.Lxyz[2]
+    ztop = z0 + Lz
+    gamma_m1 = gamma - 1.0
+    cp1 = 1.0 / P.cp
+    lnrho0 = math.log(rho0)
+    f = np.zeros((P.mvar, mz, my, mx))
+
+    # ---- lnrho: density.f90:1315-1345 ------------------------------------
+    lnr = np.full(mz, lnrho0)
+    st = {"cs2int": cs0 ** 2, "lnrhoint": lnrho0}
+
+    def poly_lnrho(mpoly, zint, zbot, zblend, isoth, fac=None):
+        stp = _step(z, zblend, widthlnrho)
+        cs2int, lnrhoint = st["cs2int"], st["lnrhoint"]
+        if isoth != 0:
+            beta1 = 0.0
+            tmp = lnrhoint + gamma * gravz / cs2int * (z - zint)
+        else:
+            beta1 = gamma * gravz / (mpoly + 1)
+            tmp = 1.0 + beta1 * (z - zint) / cs2int
+            tmp = np.maximum(tmp, EPSI)
+            tmp = lnrhoint + mpoly * np.log(tmp)
+        lnr[:] = stp * lnr + (1 - stp) * tmp
+        if isoth != 0:
+            st["lnrhoint"] = lnrhoint + gamma * gravz / cs2int * (zbot - zint)
+        else:
+            st["lnrhoint"] = lnrhoint + mpoly * math.log(1 + beta1 * (zbot - zint) / cs2int)
+        if isoth != 0 and fac is not None:
+            st["cs2int"] = fac ** 2 * cs2int
+        else:
+            st["cs2int"] = cs2int + beta1 * (zbot - zint)
+
+    poly_lnrho(mpoly2, zref, z2, ztop + Lz, isothtop, fac_cs)      # top region
+    poly_lnrho(mpoly0, z2, z1, z2, isothmid)                       # unstable layer
+    poly_lnrho(mpoly1, z1, z0, z1, 0)                              # stable layer
+
+    # ---- ss: entropy.f90:1628-1650 -----------------------------------------
+    ssz = np.zeros(mz)
+    se = {"cs2int": cs0 ** 2, "ssint": 0.0}
+
+    def poly_ss(mpoly, zint, zbot, zblend, isoth, fac=None):
+        stp = _step(z, zblend, widthss)
+        cs2int, ssint = se["cs2int"], se["ssint"]
+        if isoth != 0:
+            beta1 = 0.0
+            tmp = ssint - gamma_m1 * gravz * (z - zint) / cs2int / cp1
+        else:
+            beta1 = gamma * gravz / (mpoly + 1)
+            tmp = 1.0 + beta1 * (z - zint) / cs2int
+            tmp = np.maximum(tmp, EPSI)
+            tmp = ssint + (1 - mpoly * gamma_m1) / gamma * np.log(tmp) / cp1
+        ssz[:] = stp * ssz + (1 - stp) * tmp
+        if isoth != 0:
+            if fac is not None:
+                se["ssint"] = ssint - gamma_m1 * gravz * (zbot - zint) / cs2int / cp1 + 2 * math.log(fac) / gamma / cp1
+            else:
+                se["ssint"] = ssint - gamma_m1 * gravz * (zbot - zint) / cs2int / cp1
+        else:
+            se["ssint"] = ssint + (1 - mpoly * gamma_m1) / gamma * math.log(1 + beta1 * (zbot - zint) / cs2int) / cp1
+        if isoth != 0 and fac is not None:
+            se["cs2int"] = fac ** 2 * cs2int
+        else:
+            se["cs2int"] = cs2int + beta1 * (zbot - zint)
+
+    poly_ss(mpoly2, zref, z2, z0 + 2 * Lz, isothtop, fac_cs)
+    poly_ss(mpoly0, z2, z1, z2, isothmid)
+    poly_ss(mpoly1, z1, z0, z1, 0)
+
+    f[P.ilnrho - 1] = lnr[:, None, None]
+    f[P.iss - 1] = ssz[:, None, None]
+
+    # ---- uz: 'up-down', hydro.f90:2189-2203 ---------------------------------
+    prof = ampluu * np.exp(-0.5 * (z - z1) ** 2 / widthuu ** 2)
+    X, Y = x[None, :], y[:, None]
+    t1 = np.sqrt((X - (x0 + 0.3 * Lx)) ** 2 + (Y - (y0 + 0.3 * Ly)) ** 2)
+    t2 = np.sqrt((X - (x0 + 0.5 * Lx)) ** 2 + (Y - (y0 + 0.8 * Ly)) ** 2)
+    uz = prof[:, None, None] * np.exp(-0.5 * t1 ** 2 / widthuu ** 2)[None]
+    uz = uz - 0.7 * prof[:, None, None] * np.exp(-0.5 * t2 ** 2 / widthuu ** 2)[None]
+    f[P.iuz - 1] = uz
+    # start.x fills only the interior; ghost zones are set by the boundary conditions in run.x
+    g = np.zeros_like(f)
+    g[:, 3:-3, 3:-3, 3:-3] = f[:, 3:-3, 3:-3, 3:-3]
+    return g

@@ -163,3 +163,29 @@ def test_two_gpu_halo_exchange_matches_oracle():
                         "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(root, "tests", "mgpu_check.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_gpu_reproduces_convslab_reference_out_double(pk, dev):
+    """the CUDA path itself against the REFERENCE's golden time series
+    (samples/conv-slab/reference.out.double, real Fortran/MPI build, 13 digits)"""
+    from oracle import initcond
+    from tests.test_oracle_convslab import read_golden
+    gold = read_golden()
+    P, zprof, grid = pk.setups.config_convslab(32, 32, 32)
+    f = initcond.convslab_initial_condition(P, grid)
+    dev.initialize_GPU(P, zprof)
+    dev.register_GPU(f)
+    nw = P.nx * P.ny * P.nz
+    t, rows = 0.0, []
+    for it in range(41):
+        for isub in (1, 2, 3):
+            dt = dev.rhs_GPU(f, isub, ldiagnos=(isub == 1 and it % 10 == 0))
+        if it % 10 == 0:
+            n = dev.diagnostics()
+            rows.append([it, t, dt, np.sqrt(n["u2sum"] / nw), np.sqrt(n["u2max"]), n["rhosum"] / nw, n["sssum"] / nw,
+                         dt * n["dtc"], dt * n["dtu"], dt * n["dtnu"], dt * n["dtchi"]])
+        t += dt
+    got = np.array(rows)
+    rel = np.abs(got[:, 1:] - gold[:, 1:]) / np.maximum(np.abs(gold[:, 1:]), 1e-300)
+    rel[0, 0] = abs(got[0, 1])       # t=0 exactly
+    assert rel.max() < 2e-11, rel
