@@ -499,18 +499,36 @@ __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned coun
 { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count)); }
 __device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
 { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory"); }
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long *bar, unsigned parity)
 {
+  unsigned ok;
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra.uni WAIT_DONE;\n"
-      "bra.uni WAIT_LOOP;\n"
-      "WAIT_DONE:\n"
-      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
 }
+__device__ __forceinline__ bool mbar_test_wait(unsigned long long *bar, unsigned parity)   // non-blocking probe
+{
+  unsigned ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+  // bounded spin: a protocol error traps instead of hanging the GPU
+  for (unsigned it = 0; it < (1u << 28); it++) if (mbar_try_wait(bar, parity)) return;
+  __trap();
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{ asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory"); }
 __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, int x, int y, int z, unsigned long long *bar)
 {
   asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
@@ -566,25 +584,30 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
   const int tb = (ty + NG) * HX + tx + NG;
   const bool ww = a.write_w != 0 && active, wf = a.write_f != 0 && active;
 
+  // bar[0] = "full": phase 0 is the prologue load, phase q+1 the planes issued in step q.
+  // bar[1] = "empty": phase q completes when all NTHR threads are done with step q.
+  // No __syncthreads in the z loop: warps drift up to one plane apart.
+  unsigned long long *full = bar, *empty = bar + 1;
   if (tid == 0) {
-    mbar_init(bar, 1);
+    mbar_init(full, 1);
+    mbar_init(empty, NTHR);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
   // prologue: ring planes zb..zb+6 (padded) -> slots 0..6, plain plane zb+NG -> slot 0
   if (tid == 0) {
-    mbar_expect_tx(bar, (unsigned)((NRF * 7 + NPF) * BOX_BYTES));
+    mbar_expect_tx(full, (unsigned)((NRF * 7 + NPF) * BOX_BYTES));
 #pragma unroll 1
     for (int q = 0; q < 7; q++)
 #pragma unroll
       for (int r = 0; r < 6; r++) {
         if (!role_present<MAG, ENT>(r)) continue;
-        tma_load_3d(ring + ((size_t)r * NSLOT + q) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + q, bar);
+        tma_load_3d(ring + ((size_t)r * NSLOT + q) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + q, full);
       }
 #pragma unroll
     for (int r = 6; r < NROLE; r++) {
       if (!role_present<MAG, ENT>(r)) continue;
-      tma_load_3d(plain + ((size_t)(r - 6) * 2) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + NG, bar);
+      tma_load_3d(plain + ((size_t)(r - 6) * 2) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + NG, full);
     }
   }
   TmaAcc<MAG, ENT> acc;
@@ -601,30 +624,35 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
 #pragma unroll
   for (int q = 0; q < NRED; q++) red[q] = 0.0;
   const double beta_dt = a.write_f ? a.beta * a.dt_dev[0] : 0.0;
-  unsigned phase = 0;
-  mbar_wait(bar, phase);
-  phase ^= 1;
+  mbar_wait(full, 0);
+  // stage the planes of step q0+1 (ring: padded plane n+7, plain: padded plane n+NG+1); they
+  // overwrite the slots of step q0-1, so the elected thread first waits for "empty" phase q0-1
+  auto issue = [&](int n, int q0) {
+    mbar_expect_tx(full, (unsigned)((NRF + NPF) * BOX_BYTES));
+    const int sl = (q0 + 7) & (NSLOT - 1);
+#pragma unroll
+    for (int r = 0; r < 6; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+      tma_load_3d(ring + ((size_t)r * NSLOT + sl) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + n + 7, full);
+    }
+    const int ps = (q0 + 1) & 1;
+#pragma unroll
+    for (int r = 6; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+      tma_load_3d(plain + ((size_t)(r - 6) * 2 + ps) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + n + NG + 1, full);
+    }
+  };
 
 #pragma unroll 1
   for (int n = zb; n < ze; n++) {
     const int q0 = n - zb;
     const bool more = n + 1 < ze;
-    // 1. the TMA unit stages the next planes (ring: padded plane n+7, plain: padded plane n+NG+1)
+    bool issued = true;
     if (more) {
       if (tid == 0) {
-        mbar_expect_tx(bar, (unsigned)((NRF + NPF) * BOX_BYTES));
-        const int sl = (q0 + 7) & (NSLOT - 1);
-#pragma unroll
-        for (int r = 0; r < 6; r++) {
-          if (!role_present<MAG, ENT>(r)) continue;
-          tma_load_3d(ring + ((size_t)r * NSLOT + sl) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + n + 7, bar);
-        }
-        const int ps = (q0 + 1) & 1;
-#pragma unroll
-        for (int r = 6; r < NROLE; r++) {
-          if (!role_present<MAG, ENT>(r)) continue;
-          tma_load_3d(plain + ((size_t)(r - 6) * 2 + ps) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + n + NG + 1, bar);
-        }
+        // try once without blocking; if the slowest warp is still in step q0-1, retry after the stencils
+        issued = q0 == 0 || mbar_test_wait(empty, (unsigned)((q0 - 1) & 1));
+        if (issued) issue(n, q0);
       }
 #pragma unroll
       for (int r = 6; r < NROLE; r++) {
@@ -649,6 +677,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
     double rhs[NROLE];
     CellAux aux;
     rhs_cell<MAG, ENT, (AUXM > 0)>(acc, c, n, rhs, aux);
+    if (tid == 0 && !issued) { mbar_wait(empty, (unsigned)((q0 - 1) & 1)); issue(n, q0); }
     // 3. 2N-RK3 update (timestep.f90:119-122,162-163); f_in(cell) is the window centre
 #pragma unroll
     for (int r = 0; r < NROLE; r++) {
@@ -669,9 +698,9 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
         red[RS_AB] += aux.ab; red[RS_JB] += aux.jb; red[RS_OU] += aux.ou;
       }
     }
-    // 4. next planes have landed; everybody is done with the oldest plane
-    if (more) { mbar_wait(bar, phase); phase ^= 1; }
-    __syncthreads();
+    // 4. next planes have landed -> shift the z window, then release step q0's slots
+    if (!more) break;
+    mbar_wait(full, (unsigned)((q0 + 1) & 1));
 #pragma unroll
     for (int r = 0; r < NROLE; r++) {
       if (!role_present<MAG, ENT>(r)) continue;
@@ -680,6 +709,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
       if (r < 6) acc.w[r][6] = ring[((size_t)r * NSLOT + ((q0 + 7) & (NSLOT - 1))) * PEP + tb];
       else acc.w[r][6] = wnext[r];
     }
+    mbar_arrive(empty);
   }
   if (AUXM > 0) {
     const int bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
