@@ -478,6 +478,33 @@ __global__ void bc_fill(BcArgs b)
   }
 }
 
+// All locally periodic directions in one launch (bc_per_x/y/z, boundcond.f90:1813-1961).
+// A ghost cell takes the value of the interior cell at the wrapped coordinates, which is what
+// the sequential x -> y -> z sweeps produce at edges and corners.  Sources are interior in
+// every wrapped direction and destinations are ghost in at least one, so there is no race.
+struct BcPerArgs { double *f; int wrap[3]; long long n0, n1, n2; };
+__global__ void bc_periodic(BcPerArgs b)
+{
+  const DevPar &c = c_par;
+  long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int ix, iy, iz;
+  if (t < b.n0) {                                   // x ghosts: 6 x my x mz
+    const int gx = (int)(t % 6); const long long r = t / 6;
+    iy = (int)(r % c.my); iz = (int)(r / c.my); ix = gx < NG ? gx : c.nx + gx;
+  } else if ((t -= b.n0) < b.n1) {                  // y ghosts: mx x 6 x mz
+    ix = (int)(t % c.mx); const long long r = t / c.mx;
+    const int gy = (int)(r % 6); iz = (int)(r / 6); iy = gy < NG ? gy : c.ny + gy;
+  } else if ((t -= b.n1) < b.n2) {                  // z ghosts: mx x my x 6
+    ix = (int)(t % c.mx); const long long r = t / c.mx;
+    iy = (int)(r % c.my); const int gz = (int)(r / c.my); iz = gz < NG ? gz : c.nz + gz;
+  } else return;
+  const int sx = !b.wrap[0] ? ix : (ix < NG ? ix + c.nx : (ix >= NG + c.nx ? ix - c.nx : ix));
+  const int sy = !b.wrap[1] ? iy : (iy < NG ? iy + c.ny : (iy >= NG + c.ny ? iy - c.ny : iy));
+  const int sz = !b.wrap[2] ? iz : (iz < NG ? iz + c.nz : (iz >= NG + c.nz ? iz - c.nz : iz));
+  double *p = b.f + (long long)blockIdx.y * c.mw;
+  p[(long long)iz * c.sz + (long long)iy * c.sy + ix] = p[(long long)sz * c.sz + (long long)sy * c.sy + sx];
+}
+
 
 // ------------------------------------------------------------------------
 // rhs_tma: the production z-marching kernel.  Same scheme as rhs_march, but
@@ -565,7 +592,8 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
   const DevPar &c = c_par;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   // align the tile area to 128 B (TMA destination requirement)
-  double *smem = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  // (offset arithmetic on the __shared__ symbol itself, so that the accesses stay LDS rather than generic LD)
+  double *smem = reinterpret_cast<double *>(smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u));
   constexpr int NRF = TmaCfg<MAG, ENT>::NRF, NPF = TmaCfg<MAG, ENT>::NPF;
   double *ring = smem;
   double *plain = smem + (size_t)NRF * NSLOT * PEP;

@@ -329,6 +329,29 @@ static int launch_bc(double *f, int axis, int do_lo, int do_hi)
   return PCB200_OK;
 }
 
+// periodic directions that wrap inside this rank, all in one launch
+static bool wraps_locally(int axis)
+{
+  const pcb200_params &P = g.P;
+  const int np[3] = {P.nprocx, P.nprocy, P.nprocz};
+  if (!P.lperi[axis] || np[axis] != 1) return false;
+  const int32_t (*src)[PCB200_MAXVAR] = axis == 0 ? P.bcx : (axis == 1 ? P.bcy : P.bcz);
+  for (int fc = 0; fc < 2; fc++) for (int k = 0; k < P.mvar; k++) if (src[fc][k] != PCB200_BC_P) return false;
+  return true;
+}
+static int launch_bc_periodic(double *f, bool wx, bool wy, bool wz)
+{
+  const pcb200_params &P = g.P; const DevPar &h = g.hp;
+  BcPerArgs b; b.f = f; b.wrap[0] = wx; b.wrap[1] = wy; b.wrap[2] = wz;
+  b.n0 = wx ? 6LL * h.my * h.mz : 0; b.n1 = wy ? 6LL * h.mx * h.mz : 0; b.n2 = wz ? 6LL * h.mx * h.my : 0;
+  const long long n = b.n0 + b.n1 + b.n2;
+  dim3 blk(256), grd((unsigned)((n + 255) / 256), P.mvar);
+  bc_periodic<<<grd, blk, 0, g.st>>>(b);
+  g.launches++;
+  CK(cudaGetLastError());
+  return PCB200_OK;
+}
+
 // z halo exchange between slabs (initiate/finalize_isendrcv_bdry, mpicomm.f90:1325-2047,
 // restricted to the z direction; x,y ghosts ride along because whole mx*my planes move)
 static int exchange_z(double *f)
@@ -407,11 +430,16 @@ static int do_substep(int isub, int ldiagnos)
   double *fin = g.f[g.cur], *fout = g.f[1 - g.cur];
   int rc;
   // boundary conditions in the reference order x -> y -> z (equ.f90:211-229, boundcond.f90:1283-1290)
-  if ((rc = launch_bc(fin, 0, 1, 1))) return rc;
-  if ((rc = launch_bc(fin, 1, 1, 1))) return rc;
   const bool multi = g.nranks > 1;
   const bool per_z = P.lperi[2] != 0;
-  if (!multi) { if ((rc = launch_bc(fin, 2, 1, 1))) return rc; }
+  const bool fused_xy = wraps_locally(0) && wraps_locally(1);
+  const bool fused_z = fused_xy && !multi && wraps_locally(2);
+  if (fused_xy) { if ((rc = launch_bc_periodic(fin, true, true, fused_z))) return rc; }
+  else {
+    if ((rc = launch_bc(fin, 0, 1, 1))) return rc;
+    if ((rc = launch_bc(fin, 1, 1, 1))) return rc;
+  }
+  if (!multi) { if (!fused_z) if ((rc = launch_bc(fin, 2, 1, 1))) return rc; }
   else {
     CK(cudaEventRecord(g.ev_bc, g.st));
     CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0));
