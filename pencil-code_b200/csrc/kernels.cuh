@@ -478,6 +478,26 @@ __global__ void bc_fill(BcArgs b)
   }
 }
 
+// Face packing for the x and y halo exchange (isendrcv_bdry_x, mpicomm.f90:2049-2101, and the
+// y buffers lbufyo/ubufyo, :1592-1690): NG planes of one axis over the FULL ghost-inclusive
+// extent of the other two, so that the sequential x -> y -> z exchange carries edges and
+// corners without separate corner messages.  buf layout [var][c][b][NG planes] (axis 0) or
+// [var][iz][NG][mx] (axis 1).  unpack=1 scatters buf back into f.
+struct FaceArgs { double *f; double *buf; int axis, start, unpack; };
+__global__ void face_copy(FaceArgs a)
+{
+  const DevPar &c = c_par;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long per_var = a.axis == 0 ? (long long)NG * c.my * c.mz : (long long)NG * c.mx * c.mz;
+  if (t >= per_var) return;
+  int ix, iy, iz;
+  if (a.axis == 0) { ix = a.start + (int)(t % NG); const long long r = t / NG; iy = (int)(r % c.my); iz = (int)(r / c.my); }
+  else { ix = (int)(t % c.mx); const long long r = t / c.mx; iy = a.start + (int)(r % NG); iz = (int)(r / NG); }
+  double *p = a.f + (long long)blockIdx.y * c.mw + (long long)iz * c.sz + (long long)iy * c.sy + ix;
+  double *q = a.buf + (long long)blockIdx.y * per_var + t;
+  if (a.unpack) *p = *q; else *q = *p;
+}
+
 // All locally periodic directions in one launch (bc_per_x/y/z, boundcond.f90:1813-1961).
 // A ghost cell takes the value of the interior cell at the wrapped coordinates, which is what
 // the sequential x -> y -> z sweeps produce at edges and corners.  Sources are interior in

@@ -64,6 +64,8 @@ struct Ctx {
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
   // multi-GPU
   NcclApi nccl; ncclComm_t comm = nullptr; int rank = 0, nranks = 1;
+  double *face[4] = {nullptr, nullptr, nullptr, nullptr};   // send lo/hi, recv lo/hi for the packed x,y faces
+  size_t face_elems = 0;
   std::string err;
 };
 static Ctx g;
@@ -155,8 +157,11 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   if (P.mvar < 4 || P.mvar > PCB200_MAXVAR) return fail(PCB200_EARG, "mvar out of range");
   if (P.lentropy && !P.iss) return fail(PCB200_EARG, "lentropy without iss");
   if (P.lmagnetic && !P.iax) return fail(PCB200_EARG, "lmagnetic without iax");
-  if (P.nprocx != 1 || P.nprocy != 1) return fail(PCB200_EUNSUPP, "only z-slab decomposition (nprocx=nprocy=1) is implemented");
-  if (P.nprocz != g.nranks) return fail(PCB200_EARG, "nprocz differs from the communicator size (call pcb200_comm_init first)");
+  if (P.nprocx < 1 || P.nprocy < 1 || P.nprocz < 1 || P.nprocx * P.nprocy * P.nprocz != g.nranks)
+    return fail(PCB200_EARG, "nprocx*nprocy*nprocz differs from the communicator size (call pcb200_comm_init first)");
+  // rank layout of the reference: iproc = ipx + nprocx*(ipy + nprocy*ipz) (mpicomm.f90:367-369)
+  if (P.ipx + P.nprocx * (P.ipy + P.nprocy * P.ipz) != g.rank || P.ipx < 0 || P.ipx >= P.nprocx || P.ipy < 0 || P.ipy >= P.nprocy)
+    return fail(PCB200_EARG, "ipx,ipy,ipz do not match this rank (iproc = ipx + nprocx*(ipy + nprocy*ipz))");
   CK(cudaSetDevice(g.dev));
   const bool realloc = !g.have_par || g.P.nx != P.nx || g.P.ny != P.ny || g.P.nz != P.nz || g.P.mvar != P.mvar;
   g.P = P;
@@ -196,6 +201,14 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
       CK(cudaMemsetAsync(g.zprof[q], 0, sizeof(double) * P.nz, g.st));
     }
     g.cur = 0;
+  }
+  if (P.nprocx > 1 || P.nprocy > 1) {
+    const size_t fx = P.nprocx > 1 ? (size_t)NG * h.my * h.mz * P.mvar : 0, fy = P.nprocy > 1 ? (size_t)NG * h.mx * h.mz * P.mvar : 0;
+    const size_t need = fx > fy ? fx : fy;
+    if (need > g.face_elems) {
+      for (int i = 0; i < 4; i++) { if (g.face[i]) cudaFree(g.face[i]); CK(cudaMalloc(&g.face[i], need * sizeof(double))); }
+      g.face_elems = need;
+    }
   }
   for (int q = 0; q < PCB200_NPROF; q++) h.zprof[q] = g.zprof[q];
   {
@@ -352,15 +365,27 @@ static int launch_bc_periodic(double *f, bool wx, bool wy, bool wz)
   return PCB200_OK;
 }
 
+// neighbour ranks along one axis; -1 = physical boundary (mpicomm.f90:367-420)
+static void neighbours(int axis, int *nlo, int *nhi, bool *first, bool *last)
+{
+  const pcb200_params &P = g.P;
+  const int np[3] = {P.nprocx, P.nprocy, P.nprocz};
+  int ip[3] = {P.ipx, P.ipy, P.ipz};
+  const bool per = P.lperi[axis] != 0;
+  const int me = ip[axis];
+  auto rank_of = [&](int i) { int q[3] = {ip[0], ip[1], ip[2]}; q[axis] = i; return q[0] + np[0] * (q[1] + np[1] * q[2]); };
+  *first = me == 0; *last = me == np[axis] - 1;
+  *nlo = me > 0 ? rank_of(me - 1) : (per ? rank_of(np[axis] - 1) : -1);
+  *nhi = me < np[axis] - 1 ? rank_of(me + 1) : (per ? rank_of(0) : -1);
+}
+
 // z halo exchange between slabs (initiate/finalize_isendrcv_bdry, mpicomm.f90:1325-2047,
-// restricted to the z direction; x,y ghosts ride along because whole mx*my planes move)
+// z direction; x,y ghosts ride along because whole mx*my planes move: zero packing)
 static int exchange_z(double *f)
 {
   const pcb200_params &P = g.P; const DevPar &h = g.hp;
-  const int lo = g.rank - 1, hi = g.rank + 1;
-  const bool per = P.lperi[2] != 0;
-  const int nlo = lo >= 0 ? lo : (per ? g.nranks - 1 : -1);
-  const int nhi = hi < g.nranks ? hi : (per ? 0 : -1);
+  int nlo, nhi; bool first, last;
+  neighbours(2, &nlo, &nhi, &first, &last);
   const size_t cnt = (size_t)NG * h.sz;
   NK(g.nccl.GroupStart());
   for (int k = 0; k < P.mvar; k++) {
@@ -371,6 +396,37 @@ static int exchange_z(double *f)
     if (nlo >= 0) NK(g.nccl.Recv(b, cnt, 8, nlo, g.comm, g.st_comm));                                // lower ghosts
   }
   NK(g.nccl.GroupEnd());
+  return PCB200_OK;
+}
+
+// x or y halo exchange: pack NG planes (full extent of the other axes) -> send/recv -> unpack,
+// all on the compute stream (it must finish before any stencil runs; only z overlaps)
+static int exchange_packed(double *f, int axis)
+{
+  const pcb200_params &P = g.P; const DevPar &h = g.hp;
+  int nlo, nhi; bool first, last;
+  neighbours(axis, &nlo, &nhi, &first, &last);
+  const int n = axis == 0 ? P.nx : P.ny;
+  const long long per_var = axis == 0 ? (long long)NG * h.my * h.mz : (long long)NG * h.mx * h.mz;
+  const size_t cnt = (size_t)per_var * P.mvar;
+  dim3 blk(256), grd((unsigned)((per_var + 255) / 256), P.mvar);
+  auto copy = [&](double *buf, int start, int unpack) {
+    FaceArgs a; a.f = f; a.buf = buf; a.axis = axis; a.start = start; a.unpack = unpack;
+    face_copy<<<grd, blk, 0, g.st>>>(a);
+    g.launches++;
+  };
+  if (nlo >= 0) copy(g.face[0], NG, 0);          // lowest interior planes
+  if (nhi >= 0) copy(g.face[1], n, 0);           // highest interior planes
+  CK(cudaGetLastError());
+  NK(g.nccl.GroupStart());
+  if (nlo >= 0) NK(g.nccl.Send(g.face[0], cnt, 8, nlo, g.comm, g.st));
+  if (nhi >= 0) NK(g.nccl.Recv(g.face[3], cnt, 8, nhi, g.comm, g.st));
+  if (nhi >= 0) NK(g.nccl.Send(g.face[1], cnt, 8, nhi, g.comm, g.st));
+  if (nlo >= 0) NK(g.nccl.Recv(g.face[2], cnt, 8, nlo, g.comm, g.st));
+  NK(g.nccl.GroupEnd());
+  if (nhi >= 0) copy(g.face[3], NG + n, 1);      // upper ghosts
+  if (nlo >= 0) copy(g.face[2], 0, 1);           // lower ghosts
+  CK(cudaGetLastError());
   return PCB200_OK;
 }
 
@@ -429,27 +485,42 @@ static int do_substep(int isub, int ldiagnos)
   const pcb200_params &P = g.P;
   double *fin = g.f[g.cur], *fout = g.f[1 - g.cur];
   int rc;
-  // boundary conditions in the reference order x -> y -> z (equ.f90:211-229, boundcond.f90:1283-1290)
-  const bool multi = g.nranks > 1;
-  const bool per_z = P.lperi[2] != 0;
-  const bool fused_xy = wraps_locally(0) && wraps_locally(1);
-  const bool fused_z = fused_xy && !multi && wraps_locally(2);
-  if (fused_xy) { if ((rc = launch_bc_periodic(fin, true, true, fused_z))) return rc; }
-  else {
-    if ((rc = launch_bc(fin, 0, 1, 1))) return rc;
-    if ((rc = launch_bc(fin, 1, 1, 1))) return rc;
-  }
-  if (!multi) { if (!fused_z) if ((rc = launch_bc(fin, 2, 1, 1))) return rc; }
-  else {
-    CK(cudaEventRecord(g.ev_bc, g.st));
-    CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0));
-    if ((rc = exchange_z(fin))) return rc;
-    CK(cudaEventRecord(g.ev_halo, g.st_comm));
-    if (!per_z) {      // physical boundaries on the first/last slab only (lfirst_proc_z/llast_proc_z)
-      const int lo = g.rank == 0, hi = g.rank == g.nranks - 1;
+  // Ghost zones, axis by axis in the reference order x -> y -> z (equ.f90:211-229,
+  // boundcond.f90:1283-1290), each over the full extent of the other axes.  Per axis: wrap
+  // locally / physical boundary condition / exchange with the neighbour ranks.  Consecutive
+  // locally periodic axes share one launch.  Only the z exchange overlaps with compute.
+  const int np[3] = {P.nprocx, P.nprocy, P.nprocz};
+  bool pend[3] = {false, false, false};
+  auto flush = [&]() -> int {
+    if (!pend[0] && !pend[1] && !pend[2]) return PCB200_OK;
+    const int r = launch_bc_periodic(fin, pend[0], pend[1], pend[2]);
+    pend[0] = pend[1] = pend[2] = false;
+    return r;
+  };
+  const bool multi = np[2] > 1;          // z decomposed: interior planes overlap with the z exchange
+  for (int axis = 0; axis < 3; axis++) {
+    if (np[axis] == 1) {
+      if (wraps_locally(axis)) { pend[axis] = true; continue; }
+      if ((rc = flush())) return rc;
+      if ((rc = launch_bc(fin, axis, 1, 1))) return rc;
+      continue;
+    }
+    if ((rc = flush())) return rc;
+    int nlo, nhi; bool lfirst, llast;
+    neighbours(axis, &nlo, &nhi, &lfirst, &llast);
+    const int lo = lfirst && nlo < 0, hi = llast && nhi < 0;     // physical boundaries (lfirst_proc_*/llast_proc_*)
+    if (axis < 2) {
+      if (lo || hi) if ((rc = launch_bc(fin, axis, lo, hi))) return rc;
+      if ((rc = exchange_packed(fin, axis))) return rc;
+    } else {
+      CK(cudaEventRecord(g.ev_bc, g.st));
+      CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0));
+      if ((rc = exchange_z(fin))) return rc;
+      CK(cudaEventRecord(g.ev_halo, g.st_comm));
       if (lo || hi) if ((rc = launch_bc(fin, 2, lo, hi))) return rc;
     }
   }
+  if ((rc = flush())) return rc;
   const bool first = isub == 1;
   const bool need_dt = first && P.ldt;
   const int auxm = first ? (ldiagnos ? 2 : (need_dt ? 1 : 0)) : 0;
@@ -480,7 +551,7 @@ static int do_substep(int isub, int ldiagnos)
     const double floor1 = P.dtmax != 0.0 ? 1.0 / P.dtmax : 0.0;
     finish_dt<<<1, 32, 0, g.st>>>(g.red_dev, floor1, g.dt_dev);
     g.launches++;
-    if (multi) {
+    if (g.nranks > 1) {
       NK(g.nccl.AllReduce(g.dt_dev + 1, g.dt_dev + 1, 1, 8, 2 /*ncclMax*/, g.comm, g.st));     // set_dt, sub.f90:3909
       set_dt_from_dt1<<<1, 32, 0, g.st>>>(g.dt_dev);
       g.launches++;
@@ -604,6 +675,8 @@ extern "C" int pcb200_finalize(void)
   if (g.f_host_pinned) { cudaHostUnregister(g.f_host); g.f_host_pinned = false; }
   g.f_host = nullptr;
   for (int q = 0; q < PCB200_NPROF; q++) { if (g.zprof[q]) cudaFree(g.zprof[q]); g.zprof[q] = nullptr; }
+  for (int i = 0; i < 4; i++) { if (g.face[i]) cudaFree(g.face[i]); g.face[i] = nullptr; }
+  g.face_elems = 0;
   if (g.comm && g.nccl.CommDestroy) { g.nccl.CommDestroy(g.comm); g.comm = nullptr; }
   g.have_par = false; g.npartials = 0; g.nranks = 1; g.rank = 0;
   return PCB200_OK;

@@ -25,15 +25,24 @@ def grid_axis(n, x0, L, periodic):
 
 
 def make_params(nxgrid, nygrid, nzgrid, *, magnetic=False, entropy=False, xyz0=(-math.pi,) * 3,
-                Lxyz=(2 * math.pi,) * 3, lperi=(1, 1, 1), nprocz=1, ipz=0, **kw):
-    """Build (Params, zprofiles, grid) for a z-slab of the global grid."""
+                Lxyz=(2 * math.pi,) * 3, lperi=(1, 1, 1), nprocz=1, ipz=0, nproc=None, iproc=None, **kw):
+    """Build (Params, zprofiles, grid) for one block of the global grid.
+
+    Decomposition as the reference (cparam.f90:18, mpicomm.f90:367-369): nproc=(nprocx,nprocy,nprocz),
+    rank iproc = ipx + nprocx*(ipy + nprocy*ipz); `nprocz=,ipz=` is the z-slab shorthand."""
     P = abi.Params()
     P.abi_version = abi.ABI_VERSION
-    assert nzgrid % nprocz == 0
-    nz = nzgrid // nprocz
-    P.nx, P.ny, P.nz = nxgrid, nygrid, nz
-    P.nprocx, P.nprocy, P.nprocz = 1, 1, nprocz
-    P.ipx, P.ipy, P.ipz = 0, 0, ipz
+    if nproc is None:
+        nproc, ip = (1, 1, nprocz), (0, 0, ipz)
+    else:
+        iproc = 0 if iproc is None else iproc
+        ip = (iproc % nproc[0], (iproc // nproc[0]) % nproc[1], iproc // (nproc[0] * nproc[1]))
+    assert nxgrid % nproc[0] == 0 and nygrid % nproc[1] == 0 and nzgrid % nproc[2] == 0
+    nx, ny, nz = nxgrid // nproc[0], nygrid // nproc[1], nzgrid // nproc[2]
+    ipz = ip[2]
+    P.nx, P.ny, P.nz = nx, ny, nz
+    P.nprocx, P.nprocy, P.nprocz = nproc
+    P.ipx, P.ipy, P.ipz = ip
     for i in range(3):
         P.lperi[i] = int(lperi[i])
         P.xyz0[i] = xyz0[i]
@@ -54,9 +63,11 @@ def make_params(nxgrid, nygrid, nzgrid, *, magnetic=False, entropy=False, xyz0=(
     P.lviscosity_heat = 1
     P.lohmic_heat = 1
     P.ldt = 1
-    x, dx = grid_axis(nxgrid, xyz0[0], Lxyz[0], lperi[0])
-    y, dy = grid_axis(nygrid, xyz0[1], Lxyz[1], lperi[1])
+    xg, dx = grid_axis(nxgrid, xyz0[0], Lxyz[0], lperi[0])
+    yg, dy = grid_axis(nygrid, xyz0[1], Lxyz[1], lperi[1])
     zg, dz = grid_axis(nzgrid, xyz0[2], Lxyz[2], lperi[2])
+    x = xg[ip[0] * nx: ip[0] * nx + nx + 2 * NG].copy()
+    y = yg[ip[1] * ny: ip[1] * ny + ny + 2 * NG].copy()
     z = zg[ipz * nz: ipz * nz + nz + 2 * NG].copy()
     P.dx, P.dy, P.dz = dx, dy, dz
     P.dx_1, P.dy_1, P.dz_1 = 1.0 / dx, 1.0 / dy, 1.0 / dz

@@ -1,5 +1,6 @@
-"""Multi-GPU parity check (run under torchrun, one rank per GPU):
-z-slab decomposition with NCCL halo exchange vs the single-domain oracle.
+"""Multi-GPU parity check (run under torchrun, one rank per GPU): every block
+decomposition nprocx x nprocy x nprocz of the world size (z-slabs, x/y faces,
+2x2x2 ...) with NCCL halo exchange vs the single-domain oracle.
 
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
       --master-port 29511 tests/mgpu_check.py
@@ -30,46 +31,56 @@ def main():
     dev.comm_init(idt.numpy().tobytes(), rank, world)
     ok = True
     nsteps = 5
-    cases = {
-        "mhd_periodic": lambda nprocz, ipz: pk.setups.make_params(32, 32, 16 * world, magnetic=True, nprocz=nprocz, ipz=ipz,
-                                                                  nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3),
-        "convslab_walls": lambda nprocz, ipz: pk.setups.config_convslab(32, 32, 16 * world, nprocz=nprocz, ipz=ipz),
-    }
-    for name, mk in cases.items():
-        P, zprof, grid = mk(world, rank)
-        f = pk.setups.synthetic_fields(P, grid)
-        if name.startswith("convslab"):
-            f[P.ilnrho - 1] *= 0.1
-        dev.initialize_GPU(P, zprof)
-        dev.register_GPU(f)
-        dts = []
-        for _ in range(nsteps):
-            for isub in (1, 2, 3):
-                dt = dev.rhs_GPU(f, isub)
-            dts.append(dt)
-        dev.copy_farray_from_GPU(f)
-        inner = torch.from_numpy(np.ascontiguousarray(f[:, 3:-3, 3:-3, 3:-3]))
-        parts = [torch.zeros_like(inner) for _ in range(world)] if rank == 0 else None
-        dist.gather(inner, parts, 0)
-        if rank == 0:
-            orc = entry.oracle()
-            Pg, zpg, gg = mk(1, 0)
-            fo = pk.setups.synthetic_fields(Pg, gg)
+    decomps = [(px, py, world // (px * py)) for px in (1, 2, 4, 8) for py in (1, 2, 4, 8)
+               if world % (px * py) == 0 and 32 // px >= 8 and 32 // py >= 8]
+    if os.environ.get("PCB200_NPROC"):
+        decomps = [tuple(int(v) for v in os.environ["PCB200_NPROC"].split(","))]
+    for nproc in decomps:
+        gz = 16 * nproc[2]
+        cases = {
+            "mhd_periodic": lambda npr, ipr: pk.setups.make_params(32, 32, gz, magnetic=True, nproc=npr, iproc=ipr,
+                                                                   nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3),
+            "convslab_walls": lambda npr, ipr: pk.setups.config_convslab(32, 32, gz, nproc=npr, iproc=ipr),
+        }
+        for name, mk in cases.items():
+            P, zprof, grid = mk(nproc, rank)
+            f = pk.setups.synthetic_fields(P, grid)
             if name.startswith("convslab"):
-                fo[Pg.ilnrho - 1] *= 0.1
-            orc.set_zprofiles(zpg)
-            dfo = np.zeros_like(fo)
-            dto, d = [], 0.0
+                f[P.ilnrho - 1] *= 0.1
+            dev.initialize_GPU(P, zprof)
+            dev.register_GPU(f)
+            dts = []
             for _ in range(nsteps):
-                d = orc.timestep(fo, dfo, Pg, d)
-                dto.append(d)
-            got = np.concatenate([p.numpy() for p in parts], axis=1)
-            ref = fo[:, 3:-3, 3:-3, 3:-3]
-            err = max(np.abs(got[k] - ref[k]).max() / max(np.abs(ref[k]).max(), 1e-300) for k in range(ref.shape[0]))
-            dterr = np.abs(np.array(dts) / np.array(dto) - 1).max()
-            good = err < 1e-12 and dterr < 1e-13
-            ok &= good
-            print(f"[mgpu] {name}: ranks={world} rel Linf={err:.3e} dt err={dterr:.3e} {'OK' if good else 'FAIL'}", flush=True)
+                for isub in (1, 2, 3):
+                    dt = dev.rhs_GPU(f, isub)
+                dts.append(dt)
+            dev.copy_farray_from_GPU(f)
+            inner = torch.from_numpy(np.ascontiguousarray(f[:, 3:-3, 3:-3, 3:-3]))
+            parts = [torch.zeros_like(inner) for _ in range(world)] if rank == 0 else None
+            dist.gather(inner, parts, 0)
+            if rank == 0:
+                orc = entry.oracle()
+                Pg, zpg, gg = mk((1, 1, 1), 0)
+                fo = pk.setups.synthetic_fields(Pg, gg)
+                if name.startswith("convslab"):
+                    fo[Pg.ilnrho - 1] *= 0.1
+                orc.set_zprofiles(zpg)
+                dfo = np.zeros_like(fo)
+                dto, d = [], 0.0
+                for _ in range(nsteps):
+                    d = orc.timestep(fo, dfo, Pg, d)
+                    dto.append(d)
+                ref = fo[:, 3:-3, 3:-3, 3:-3]
+                got = np.zeros_like(ref)
+                nz, ny, nx = inner.shape[1:]
+                for r, part in enumerate(parts):      # iproc = ipx + nprocx*(ipy + nprocy*ipz)
+                    ix, iy, iz = r % nproc[0], (r // nproc[0]) % nproc[1], r // (nproc[0] * nproc[1])
+                    got[:, iz * nz:(iz + 1) * nz, iy * ny:(iy + 1) * ny, ix * nx:(ix + 1) * nx] = part.numpy()
+                err = max(np.abs(got[k] - ref[k]).max() / max(np.abs(ref[k]).max(), 1e-300) for k in range(ref.shape[0]))
+                dterr = np.abs(np.array(dts) / np.array(dto) - 1).max()
+                good = err < 1e-12 and dterr < 1e-13
+                ok &= good
+                print(f"[mgpu] {name}: nproc={nproc} rel Linf={err:.3e} dt err={dterr:.3e} {'OK' if good else 'FAIL'}", flush=True)
     flag = torch.tensor([1 if ok else 0])
     dist.broadcast(flag, 0)
     dev.finalize_GPU()
