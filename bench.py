@@ -142,6 +142,7 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--decomp", default="", help="nprocx,nprocy,nprocz (default: z-slabs 1,1,N)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -170,8 +171,10 @@ def main():
     n = args.n
     # weak scaling: every GPU owns an n^3 slab, global box n x n x (n*world), dz kept equal
     L = 2 * np.pi
-    P, zprof, grid = pk.setups.make_params(n, n, n * world, magnetic=True, nprocz=world, ipz=rank,
-                                           Lxyz=(L, L, L * world), nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3)
+    nproc = tuple(int(v) for v in args.decomp.split(",")) if args.decomp else (1, 1, world)
+    assert nproc[0] * nproc[1] * nproc[2] == world, "--decomp does not multiply to the world size"
+    P, zprof, grid = pk.setups.make_params(n * nproc[0], n * nproc[1], n * nproc[2], magnetic=True, nproc=nproc, iproc=rank,
+                                           Lxyz=(L * nproc[0], L * nproc[1], L * nproc[2]), nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3)
     f = pk.setups.synthetic_fields(P, grid)
     dev.initialize_GPU(P, zprof)
     dev.register_GPU(f)
@@ -248,8 +251,8 @@ def main():
         "metric": "Mcell-updates/s per RK3 substep", "value": value, "unit": "Mcell-updates/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"isothermal helical-MHD box (BASELINE config 3), {n}^3 cells per GPU, mvar=7, z-slabs",
-                   "global_grid": [n, n, n * world], "step": "one RK3 time step = 3 substeps incl. BCs, CFL dt, 2N update",
+        "config": {"workload": f"isothermal helical-MHD box (BASELINE config 3), {n}^3 cells per GPU, mvar=7",
+                   "global_grid": [n * nproc[0], n * nproc[1], n * nproc[2]], "decomposition": list(nproc), "step": "one RK3 time step = 3 substeps incl. BCs, CFL dt, 2N update",
                    "l2": f"inputs larger than L2 ({f.nbytes / 1e9:.2f} GB per buffer)", "dt": dt},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if ach else None,
                      "traffic": traffic, "peak_source": peak_src, "kernel": "rhs_tma<MAG=1,ENT=0>", "launches_timed": kcount,
