@@ -216,6 +216,49 @@ int64_t pcb200_launch_count(void);
 int pcb200_rhs_kernel_time(float *avg_ms, int *count);
 int pcb200_enable_kernel_timing(int on);
 
+/* ---------------------------------------------------------------------
+ * Dust particles (particles_dust with TSC particle-mesh).
+ * The reference's GPU slot has no particle entry points (gpu_astaroth.f90:32-71
+ * refuses lparticles); these are what gpu_b200.f90 calls from rhs_GPU when
+ * lparticles is on.  Layouts are the reference's own (particles_cdata.f90):
+ *   fp(mpar_loc,mparray), dfp(mpar_loc,mpvar)  column-major, particle index
+ *   fastest; columns ixp,iyp,izp,ivpx,ivpy,ivpz = 1..6;
+ *   ipar(mpar_loc) int32; ineargrid(mpar_loc,3) int32 (1-based l,m,n incl. ghosts).
+ * Per substep the device does what pde does around the mn-loop:
+ *   particles_timestep_first  (particles_main.f90:486)  dfp = alpha*dfp
+ *   particles_boundconds      (:625)  wrap -> map_nearest_grid -> stable sort by
+ *                                      pencil index imn -> np, TSC rhop
+ *   dxxp_dt_pencil/dvvp_dt_pencil (particles_dust.f90:3918,3979): interpolation
+ *       of u (quadratic spline), drag, TSC back-reaction into df_u, CFL terms
+ *   dxxp_dt/dvvp_dt (:3120,:3199), fold_df (ghostfold_mpicomm.f90:28)
+ *   particles_timestep_second (particles_main.f90:507)  fp += dt*beta*dfp      */
+typedef struct pcb200_particle_params {
+  int32_t abi_version;
+  int32_t npar_loc;              /* live particles on this rank */
+  int32_t mpar_loc;              /* capacity = leading dimension of fp, dfp, ipar, ineargrid */
+  int32_t ldragforce_dust_par;   /* drag on the particles (particles_dust.f90:4264) */
+  int32_t ldragforce_gas_par;    /* back-reaction on the gas (:4443-4536) */
+  int32_t lcoriolis_force_par;   /* dvvp_dt Coriolis term, uses pcb200_params.Omega (:3230) */
+  int32_t ldt_adv_par;           /* particle advection CFL (dxxp_dt_pencil :3936) */
+  int32_t lcheck_exact_frontier; /* clamp ineargrid into the interior (particles_map.f90:940) */
+  int32_t reserved_i[8];
+  double tausp;                  /* constant friction time (ldraglaw_epstein, get_frictiontime :5410) */
+  double rhop_swarm;             /* mass density of one superparticle in a cell (get_rhopswarm, particles_sub.f90:950) */
+  double cdtp, cdtp_drag;        /* particles_dust.f90:59 */
+  double reserved_d[8];
+} pcb200_particle_params;
+
+/* parameters + device buffers; call after pcb200_initialize. npar_loc=0 switches particles off. */
+int pcb200_particles_initialize(const pcb200_particle_params *pp);
+/* upload particle state from the host arrays (leading dimension mpar_loc) */
+int pcb200_particles_load(const double *fp, const int32_t *ipar);
+/* download particle state; any pointer may be NULL. k1_imn/k2_imn: ny*nz entries
+ * (1-based first/last particle of each pencil in imn order, 0 if empty, particles_map.f90:1920) */
+int pcb200_particles_store(double *fp, double *dfp, int32_t *ipar, int32_t *ineargrid,
+                           int32_t *k1_imn, int32_t *k2_imn);
+/* aux fields of map_xxp_grid on the full (mx,my,mz) grid: np and rhop */
+int pcb200_particles_get_aux(double *np, double *rhop);
+
 const char *pcb200_last_error(void);
 int pcb200_abi_version(void);
 

@@ -61,6 +61,22 @@ void pcref_addforce(double *f, const pcb200_params *par, const pcb200_forcing *f
 
 int pcref_num_threads(void);
 
+/* ---- dust particles (pcref_particles.c; parity unpinned, see its header) ---- */
+void pcref_particles_boundconds(double *fp, const pcb200_params *par, const pcb200_particle_params *pp);
+void pcref_particles_map_nearest_grid(const double *fp, int32_t *ineargrid, const pcb200_params *par,
+                                      const pcb200_particle_params *pp);
+void pcref_setup_imn_array(const pcb200_params *par, int32_t *imn_array);
+void pcref_particles_sort(double *fp, double *dfp, int32_t *ipar, int32_t *ineargrid, int32_t *k1_imn, int32_t *k2_imn,
+                          const pcb200_params *par, const pcb200_particle_params *pp);
+void pcref_particles_map_xxp_grid(const double *fp, const int32_t *ineargrid, double *np, double *rhop,
+                                  const pcb200_params *par, const pcb200_particle_params *pp);
+void pcref_particles_pde(const double *f, double *df, const double *fp, double *dfp, const int32_t *ineargrid,
+                         const pcb200_params *par, const pcb200_particle_params *pp, int lfirst, double *dt1_max);
+void pcref_timestep_particles(double *f, double *df, const pcb200_params *par, const pcb200_forcing *frc,
+                              double *dt, double *diag, const pcb200_particle_params *pp,
+                              double *fp, double *dfp, int32_t *ipar, int32_t *ineargrid,
+                              double *np, double *rhop, int32_t *k1_imn, int32_t *k2_imn);
+
 #ifdef __cplusplus
 }
 #endif

@@ -12,7 +12,8 @@ LIB = os.path.join(_HERE, "libpcref.so")
 
 
 def build(force=False):
-    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(os.path.join(_HERE, "pcref.c")):
+    srcs = [os.path.join(_HERE, n) for n in ("pcref.c", "pcref_particles.c", "pcref.h")]
+    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(q) for q in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return LIB
 
@@ -40,6 +41,18 @@ class Oracle:
         L.pcref_set_zprofile.argtypes = [i, p, i]
         L.pcref_set_zprofile.restype = None
         L.pcref_num_threads.restype = i
+        PP, PA = C.POINTER(abi.ParticleParams), C.POINTER(abi.Params)
+        L.pcref_particles_boundconds.argtypes = [p, PA, PP]
+        L.pcref_particles_map_nearest_grid.argtypes = [p, p, PA, PP]
+        L.pcref_setup_imn_array.argtypes = [PA, p]
+        L.pcref_particles_sort.argtypes = [p, p, p, p, p, p, PA, PP]
+        L.pcref_particles_map_xxp_grid.argtypes = [p, p, p, p, PA, PP]
+        L.pcref_particles_pde.argtypes = [p, p, p, p, p, PA, PP, i, C.POINTER(d)]
+        L.pcref_timestep_particles.argtypes = [p, p, PA, C.POINTER(abi.Forcing), C.POINTER(d), p, PP, p, p, p, p, p, p, p, p]
+        for name in ("pcref_particles_boundconds", "pcref_particles_map_nearest_grid", "pcref_setup_imn_array",
+                     "pcref_particles_sort", "pcref_particles_map_xxp_grid", "pcref_particles_pde",
+                     "pcref_timestep_particles"):
+            getattr(L, name).restype = None
 
     def set_zprofiles(self, zprof):
         for which, arr in (zprof or {}).items():
@@ -85,3 +98,39 @@ class Oracle:
 
     def num_threads(self):
         return self.lib.pcref_num_threads()
+
+    # ---- dust particles (pcref_particles.c) ----------------------------------
+    def imn_array(self, par):
+        out = np.zeros(par.ny * par.nz, dtype=np.int32)
+        self.lib.pcref_setup_imn_array(C.byref(par), out.ctypes.data)
+        return out.reshape(par.nz, par.ny)
+
+    def particles_boundconds(self, st, par, pp):
+        self.lib.pcref_particles_boundconds(st.fp.ctypes.data, C.byref(par), C.byref(pp))
+
+    def particles_map_nearest_grid(self, st, par, pp):
+        self.lib.pcref_particles_map_nearest_grid(st.fp.ctypes.data, st.ineargrid.ctypes.data, C.byref(par), C.byref(pp))
+
+    def particles_sort(self, st, par, pp):
+        self.lib.pcref_particles_sort(st.fp.ctypes.data, st.dfp.ctypes.data, st.ipar.ctypes.data, st.ineargrid.ctypes.data,
+                                      st.k1_imn.ctypes.data, st.k2_imn.ctypes.data, C.byref(par), C.byref(pp))
+
+    def particles_map_xxp_grid(self, st, par, pp):
+        self.lib.pcref_particles_map_xxp_grid(st.fp.ctypes.data, st.ineargrid.ctypes.data, st.np_.ctypes.data,
+                                              st.rhop.ctypes.data, C.byref(par), C.byref(pp))
+
+    def particles_pde(self, f, df, st, par, pp, lfirst=True, dt1_max=0.0):
+        d = C.c_double(dt1_max)
+        self.lib.pcref_particles_pde(f.ctypes.data, df.ctypes.data, st.fp.ctypes.data, st.dfp.ctypes.data,
+                                     st.ineargrid.ctypes.data, C.byref(par), C.byref(pp), int(lfirst), C.byref(d))
+        return d.value
+
+    def timestep_particles(self, f, df, par, pp, st, dt=0.0, frc=None, diag=None):
+        d = C.c_double(dt)
+        self.lib.pcref_timestep_particles(f.ctypes.data, df.ctypes.data, C.byref(par),
+                                          C.byref(frc) if frc is not None else None, C.byref(d),
+                                          diag.ctypes.data if diag is not None else None, C.byref(pp),
+                                          st.fp.ctypes.data, st.dfp.ctypes.data, st.ipar.ctypes.data,
+                                          st.ineargrid.ctypes.data, st.np_.ctypes.data, st.rhop.ctypes.data,
+                                          st.k1_imn.ctypes.data, st.k2_imn.ctypes.data)
+        return d.value

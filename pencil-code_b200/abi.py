@@ -67,6 +67,19 @@ class Forcing(C.Structure):
     ]
 
 
+class ParticleParams(C.Structure):
+    """pcb200_particle_params (particles_dust/particles_map run parameters)."""
+    _fields_ = [
+        ("abi_version", _i),
+        ("npar_loc", _i), ("mpar_loc", _i),
+        ("ldragforce_dust_par", _i), ("ldragforce_gas_par", _i), ("lcoriolis_force_par", _i),
+        ("ldt_adv_par", _i), ("lcheck_exact_frontier", _i),
+        ("reserved_i", _i * 8),
+        ("tausp", _d), ("rhop_swarm", _d), ("cdtp", _d), ("cdtp_drag", _d),
+        ("reserved_d", _d * 8),
+    ]
+
+
 # every symbol include/pcb200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "pcb200_init": (C.c_int, [C.c_int]),
@@ -88,6 +101,10 @@ SYMBOLS = {
     "pcb200_launch_count": (C.c_int64, []),
     "pcb200_rhs_kernel_time": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "pcb200_enable_kernel_timing": (C.c_int, [C.c_int]),
+    "pcb200_particles_initialize": (C.c_int, [C.POINTER(ParticleParams)]),
+    "pcb200_particles_load": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "pcb200_particles_store": (C.c_int, [C.c_void_p] * 6),
+    "pcb200_particles_get_aux": (C.c_int, [C.c_void_p, C.c_void_p]),
     "pcb200_last_error": (C.c_char_p, []),
     "pcb200_abi_version": (C.c_int, []),
 }

@@ -209,3 +209,65 @@ def config_convslab(nxgrid=32, nygrid=32, nzgrid=32, nprocz=1, ipz=0, **kw):
     )
     d.update(kw)
     return make_params(nxgrid, nygrid, nzgrid, entropy=True, nprocz=nprocz, ipz=ipz, **d)
+
+
+# ---------------------------------------------------------------------------
+# dust particles (BASELINE config 5)
+class ParticleState:
+    """Host-side particle arrays in the reference's layout (particles_cdata.f90):
+    fp(mpar_loc,mparray), dfp(mpar_loc,mpvar) -> [6][mpar_loc]; ipar; ineargrid [3][mpar_loc];
+    np/rhop aux fields (mz,my,mx); k1_imn/k2_imn (ny*nz)."""
+
+    def __init__(self, P, npar, mpar=None):
+        mpar = npar if mpar is None else mpar
+        self.npar, self.mpar = npar, mpar
+        self.fp = np.zeros((6, mpar))
+        self.dfp = np.zeros((6, mpar))
+        self.ipar = np.zeros(mpar, dtype=np.int32)
+        self.ineargrid = np.zeros((3, mpar), dtype=np.int32)
+        shape = (P.nz + 2 * NG, P.ny + 2 * NG, P.nx + 2 * NG)
+        self.np_ = np.zeros(shape)
+        self.rhop = np.zeros(shape)
+        self.k1_imn = np.zeros(P.ny * P.nz, dtype=np.int32)
+        self.k2_imn = np.zeros(P.ny * P.nz, dtype=np.int32)
+
+    def copy(self):
+        import copy
+        return copy.deepcopy(self)
+
+
+def make_particle_params(P, npar, mpar=None, *, tausp=0.1, eps_dtog=0.5, backreaction=True, **kw):
+    """particles_run_pars: constant friction time (ldraglaw_epstein with tausp), TSC mesh,
+    rhop_swarm from eps_dtog as particles_dust.f90:830-850 does for a uniform gas of density
+    rho0=exp(lnrho0): rhop_swarm = eps_dtog*rho0/(npar/nwgrid)."""
+    pp = abi.ParticleParams()
+    pp.abi_version = abi.ABI_VERSION
+    pp.npar_loc = npar
+    pp.mpar_loc = npar if mpar is None else mpar
+    pp.ldragforce_dust_par = 1
+    pp.ldragforce_gas_par = int(backreaction)
+    pp.lcoriolis_force_par = 1
+    pp.ldt_adv_par = 1
+    pp.lcheck_exact_frontier = 1
+    pp.tausp = tausp
+    nw = P.nx * P.nprocx * P.ny * P.nprocy * P.nz * P.nprocz
+    npar_glob = npar * P.nprocx * P.nprocy * P.nprocz
+    pp.rhop_swarm = eps_dtog * math.exp(P.lnrho0) / (npar_glob / nw)
+    pp.cdtp, pp.cdtp_drag = 0.2, 0.2
+    for name, val in kw.items():
+        if not hasattr(pp, name):
+            raise KeyError(name)
+        setattr(pp, name, val)
+    return pp
+
+
+def synthetic_particles(P, pp, seed=4321, vampl=0.05):
+    """Uniform random positions in the (global) box, small random velocities; ipar = 1..npar."""
+    rng = np.random.default_rng(seed)
+    st = ParticleState(P, pp.npar_loc, pp.mpar_loc)
+    n = pp.npar_loc
+    for j in range(3):
+        st.fp[j, :n] = P.xyz0[j] + P.Lxyz[j] * rng.random(n)
+        st.fp[3 + j, :n] = vampl * rng.standard_normal(n)
+    st.ipar[:n] = np.arange(1, n + 1, dtype=np.int32)
+    return st
