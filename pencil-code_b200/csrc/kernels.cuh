@@ -381,9 +381,14 @@ __global__ void axpy_update(const double *__restrict__ f_in, const double *__res
 }
 
 // dt = 1/max(dt1, 1/dtmax) (equ.f90:280-290, sub.f90:3911) from the reduced partials
-__global__ void finish_dt(const double *__restrict__ red, double dt1_floor, double *__restrict__ dt_dev)
+// extra: optional second contribution to dt1_max (the particle CFL terms)
+__global__ void finish_dt(const double *__restrict__ red, double dt1_floor, double *__restrict__ dt_dev, const double *__restrict__ extra)
 {
-  if (threadIdx.x == 0) { const double d = fmax(red[RD_DT1], dt1_floor); dt_dev[1] = d; dt_dev[0] = 1.0 / d; }
+  if (threadIdx.x == 0) {
+    double d = fmax(red[RD_DT1], dt1_floor);
+    if (extra) d = fmax(d, extra[0]);
+    dt_dev[1] = d; dt_dev[0] = 1.0 / d;
+  }
 }
 __global__ void set_dt_from_dt1(double *__restrict__ dt_dev)   // after the cross-rank max of dt_dev[1]
 {

@@ -1,0 +1,293 @@
+// particles.cuh -- dust particles on the device.
+//
+// What pde does around the mn-loop when lparticles is on, one kernel per stage:
+//   part_first        particles_timestep_first   (particles_main.f90:486-498)
+//   part_bc_map       boundconds_particles 'p'   (particles_sub.f90:170-215) + map_nearest_grid
+//                     (particles_map.f90:895-984; inverse_grid, grid.f90:2310-2343) + sort key
+//   [stable radix sort of (key, index) by the pencil index imn, particles_map.f90:986-1163]
+//   part_gather       fp, dfp, ipar, ineargrid permuted into pencil order
+//   part_pencil_bounds  k1_imn, k2_imn             (particles_map.f90:1920-1948)
+//   part_map_xxp      np and TSC rhop               (particles_map.f90:1295-1742)
+//   part_drag         dxxp_dt_pencil/dvvp_dt_pencil (particles_dust.f90:3918-4911): spline
+//                     interpolation of u, drag, TSC back-reaction, CFL; dxxp_dt, dvvp_dt (:3120,:3199)
+//   part_dt_cells     dt1_drag per cell             (particles_dust.f90:4843-4910)
+//   part_backreact    adds the deposited drag to the 2N register / new state of u
+//   part_second       particles_timestep_second  (particles_main.f90:521)
+// Layout = the reference's: fp[6][mpar] (particle index fastest), ineargrid[3][mpar] 1-based.
+// Deposits wrap at scatter time in locally periodic directions, which is fold_df/fold_f
+// (ghostfold_mpicomm.f90:46-124) without the intermediate ghost layer.
+#pragma once
+
+struct PartPar {
+  int npar, mpar;
+  int ldrag_dust, ldrag_gas, lcoriolis, ldt_adv;
+  int wrap[3];                 // direction wraps inside this rank (fold == periodic index wrap)
+  int lperi[3], shift[3];      // shift = n*ip (grid.f90:2291-2300)
+  double xyz0[3], Lxyz[3], h[3], h_1[3], x0_loc[3];
+  double tausp1, rhop_swarm, cdtp, cdtp_drag, Omega2;
+  int iux, ilnrho;             // storage slots (0-based)
+};
+
+__global__ void part_first(double *__restrict__ dfp, int npar, int mpar, double alpha)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= npar) return;
+#pragma unroll
+  for (int j = 0; j < 6; j++) dfp[(size_t)j * mpar + k] = alpha == 0.0 ? 0.0 : alpha * dfp[(size_t)j * mpar + k];
+}
+
+// NINT = round half away from zero = round() (not rint)
+__device__ __forceinline__ int part_nearest(const PartPar &q, int ax, int nloc, double x)
+{
+  double xi = (x - q.xyz0[ax]) / q.h[ax];
+  xi = q.lperi[ax] ? xi + (double)NG + 0.5 : xi + (double)(NG + 1);
+  xi = xi - (double)q.shift[ax];
+  const int inear = (int)round(xi);
+  const double xyz1 = q.xyz0[ax] + q.Lxyz[ax];
+  if ((x < xyz1 && inear > NG + nloc) || (x < q.xyz0[ax] && inear > NG)) xi = ::nextafter(xi, -1.0e308);
+  int i = (int)round(xi);
+  return min(max(i, NG + 1), NG + nloc);           // lcheck_exact_frontier (particles_map.f90:940-943)
+}
+
+__global__ void part_bc_map(PartPar q, double *__restrict__ fp, int *__restrict__ inear, const int *__restrict__ imn_array,
+                            unsigned *__restrict__ keys, unsigned *__restrict__ vals)
+{
+  const DevPar &c = c_par;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= q.npar) return;
+  const int nloc[3] = {c.nx, c.ny, c.nz};
+  int idx[3];
+#pragma unroll
+  for (int ax = 0; ax < 3; ax++) {
+    double x = fp[(size_t)ax * q.mpar + k];
+    // bcpx=bcpy=bcpz='p' (the particle boundary condition, independent of the gas one)
+    if (x < q.xyz0[ax]) x = x + q.Lxyz[ax];
+    if (x >= q.xyz0[ax] + q.Lxyz[ax]) x = x - q.Lxyz[ax];
+    fp[(size_t)ax * q.mpar + k] = x;
+    idx[ax] = part_nearest(q, ax, nloc[ax], x);
+    inear[(size_t)ax * q.mpar + k] = idx[ax];
+  }
+  keys[k] = (unsigned)(imn_array[(idx[2] - NG - 1) * c.ny + (idx[1] - NG - 1)] - 1);
+  vals[k] = (unsigned)k;
+}
+
+__global__ void part_gather(int npar, int mpar, const unsigned *__restrict__ perm,
+                            const double *__restrict__ fp_in, double *__restrict__ fp_out,
+                            const double *__restrict__ dfp_in, double *__restrict__ dfp_out,
+                            const int *__restrict__ ipar_in, int *__restrict__ ipar_out,
+                            const int *__restrict__ in_in, int *__restrict__ in_out)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= npar) return;
+  const unsigned s = perm[k];
+#pragma unroll
+  for (int j = 0; j < 6; j++) {
+    fp_out[(size_t)j * mpar + k] = fp_in[(size_t)j * mpar + s];
+    dfp_out[(size_t)j * mpar + k] = dfp_in[(size_t)j * mpar + s];
+  }
+#pragma unroll
+  for (int j = 0; j < 3; j++) in_out[(size_t)j * mpar + k] = in_in[(size_t)j * mpar + s];
+  ipar_out[k] = ipar_in[s];
+}
+
+__global__ void part_pencil_bounds(int npar, const unsigned *__restrict__ keys, int *__restrict__ k1, int *__restrict__ k2)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= npar) return;
+  const unsigned key = keys[k];
+  if (k == 0 || keys[k - 1] != key) k1[key] = k + 1;
+  if (k == npar - 1 || keys[k + 1] != key) k2[key] = k + 1;
+}
+
+// TSC weight of grid point ixx (0-based) for a particle at xp with nearest point ix0
+// (particles_dust.f90:4467-4490)
+__device__ __forceinline__ double part_tsc(const PartPar &q, int ax, double xp, int ixx, int ix0)
+{
+  const double xg = q.x0_loc[ax] + (ixx - NG) * q.h[ax];
+  if (ixx != ix0) { const double a = fabs(xp - xg) * q.h_1[ax]; return 1.125 - 1.5 * a + 0.5 * (a * a); }
+  const double b = (xp - xg) * q.h_1[ax];
+  return 0.75 - b * b;
+}
+// index of a deposit target: wrapped back into the interior where the direction folds locally
+__device__ __forceinline__ int part_fold(int i, int n, int wrap)
+{
+  if (!wrap) return i;
+  return i < NG ? i + n : (i >= NG + n ? i - n : i);
+}
+
+__global__ void part_map_xxp(PartPar q, const double *__restrict__ fp, const int *__restrict__ inear,
+                             int *__restrict__ np_i, double *__restrict__ rhop)
+{
+  const DevPar &c = c_par;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= q.npar) return;
+  const int i0[3] = {inear[k] - 1, inear[(size_t)q.mpar + k] - 1, inear[(size_t)2 * q.mpar + k] - 1};
+  const double xp[3] = {fp[k], fp[(size_t)q.mpar + k], fp[(size_t)2 * q.mpar + k]};
+  atomicAdd(&np_i[(long long)i0[2] * c.sz + (long long)i0[1] * c.sy + i0[0]], 1);
+  double wx[3], wy[3], wz[3];
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    wx[d] = part_tsc(q, 0, xp[0], i0[0] + d - 1, i0[0]);
+    wy[d] = part_tsc(q, 1, xp[1], i0[1] + d - 1, i0[1]);
+    wz[d] = part_tsc(q, 2, xp[2], i0[2] + d - 1, i0[2]);
+  }
+#pragma unroll
+  for (int dz = 0; dz < 3; dz++) {
+    const long long oz = (long long)part_fold(i0[2] + dz - 1, c.nz, q.wrap[2]) * c.sz;
+#pragma unroll
+    for (int dy = 0; dy < 3; dy++) {
+      const long long oy = oz + (long long)part_fold(i0[1] + dy - 1, c.ny, q.wrap[1]) * c.sy;
+#pragma unroll
+      for (int dx = 0; dx < 3; dx++)
+        atomicAdd(&rhop[oy + part_fold(i0[0] + dx - 1, c.nx, q.wrap[0])], (wx[dx] * wy[dy]) * wz[dz]);
+    }
+  }
+}
+
+__device__ __forceinline__ void atomic_max_nonneg(double *addr, double v)   // exact for v >= 0
+{ atomicMax(reinterpret_cast<unsigned long long *>(addr), (unsigned long long)__double_as_longlong(v)); }
+
+// One thread per particle.  f = state of this substep with valid ghost zones; dfu[3][mw]
+// receives the back-reaction (zeroed before the launch); dt1 (one double) takes the
+// advective particle CFL term when ldt.
+__global__ void __launch_bounds__(128) part_drag(PartPar q, const double *__restrict__ f, const double *__restrict__ fp,
+                                                  double *__restrict__ dfp, const int *__restrict__ inear,
+                                                  double *__restrict__ dfu, double *__restrict__ dt1, int ldt)
+{
+  const DevPar &c = c_par;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  double v_adv = 0.0;
+  if (k < q.npar) {
+    const size_t M = q.mpar;
+    const int i0[3] = {inear[k] - 1, inear[M + k] - 1, inear[2 * M + k] - 1};
+    const double xp[3] = {fp[k], fp[M + k], fp[2 * M + k]};
+    const double vp[3] = {fp[3 * M + k], fp[4 * M + k], fp[5 * M + k]};
+    if (ldt && q.ldt_adv) {                                         // dxxp_dt_pencil :3936-3968
+      const double ax = fabs(vp[0]) * q.h_1[0], ay = fabs(vp[1]) * q.h_1[1], az = fabs(vp[2]) * q.h_1[2];
+      v_adv = sqrt(ax * ax + ay * ay + az * az) / q.cdtp;
+    }
+    double dvp[3] = {0.0, 0.0, 0.0};
+    if (q.ldrag_dust) {
+      // quadratic spline interpolation of u (particles_map.f90:686-722)
+      double sx[3], sy[3], sz[3];
+      {
+        const double d0 = (xp[0] - (q.x0_loc[0] + (i0[0] - NG) * q.h[0])) * q.h_1[0];
+        const double d1 = (xp[1] - (q.x0_loc[1] + (i0[1] - NG) * q.h[1])) * q.h_1[1];
+        const double d2 = (xp[2] - (q.x0_loc[2] + (i0[2] - NG) * q.h[2])) * q.h_1[2];
+        sx[0] = 0.5 * ((0.5 - d0) * (0.5 - d0)); sx[1] = 0.75 - d0 * d0; sx[2] = 0.5 * ((0.5 + d0) * (0.5 + d0));
+        sy[0] = 0.5 * ((0.5 - d1) * (0.5 - d1)); sy[1] = 0.75 - d1 * d1; sy[2] = 0.5 * ((0.5 + d1) * (0.5 + d1));
+        sz[0] = 0.5 * ((0.5 - d2) * (0.5 - d2)); sz[1] = 0.75 - d2 * d2; sz[2] = 0.5 * ((0.5 + d2) * (0.5 + d2));
+      }
+      const long long c0 = (long long)i0[2] * c.sz + (long long)i0[1] * c.sy + i0[0];
+      double uup[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+      for (int dz = 0; dz < 3; dz++)
+#pragma unroll
+        for (int dy = 0; dy < 3; dy++) {
+          const double wyz = sy[dy] * sz[dz];
+          const long long o = c0 + (long long)(dz - 1) * c.sz + (long long)(dy - 1) * c.sy;
+#pragma unroll
+          for (int dx = 0; dx < 3; dx++) {
+            const double w = sx[dx] * wyz;
+#pragma unroll
+            for (int j = 0; j < 3; j++) uup[j] += w * __ldg(f + (long long)(q.iux + j) * c.mw + o + dx - 1);
+          }
+        }
+      double drag[3];
+#pragma unroll
+      for (int j = 0; j < 3; j++) { drag[j] = -q.tausp1 * (vp[j] - uup[j]); dvp[j] = drag[j]; }   // :4264
+      if (q.ldrag_gas) {                                            // TSC back-reaction :4443-4536
+        double wx[3], wy[3], wz[3];
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+          wx[d] = part_tsc(q, 0, xp[0], i0[0] + d - 1, i0[0]);
+          wy[d] = part_tsc(q, 1, xp[1], i0[1] + d - 1, i0[1]);
+          wz[d] = part_tsc(q, 2, xp[2], i0[2] + d - 1, i0[2]);
+        }
+        const double *lnrho = f + (long long)q.ilnrho * c.mw;
+#pragma unroll
+        for (int dz = 0; dz < 3; dz++)
+#pragma unroll
+          for (int dy = 0; dy < 3; dy++)
+#pragma unroll
+            for (int dx = 0; dx < 3; dx++) {
+              // gas density at the (unfolded) target: ghost zones of f hold the periodic image
+              const long long src = c0 + (long long)(dz - 1) * c.sz + (long long)(dy - 1) * c.sy + dx - 1;
+              const long long dst = (long long)part_fold(i0[2] + dz - 1, c.nz, q.wrap[2]) * c.sz
+                                  + (long long)part_fold(i0[1] + dy - 1, c.ny, q.wrap[1]) * c.sy
+                                  + part_fold(i0[0] + dx - 1, c.nx, q.wrap[0]);
+              const double fac = -q.rhop_swarm * exp(-__ldg(lnrho + src)) * ((wx[dx] * wy[dy]) * wz[dz]);
+#pragma unroll
+              for (int j = 0; j < 3; j++) atomicAdd(dfu + (long long)j * c.mw + dst, fac * drag[j]);
+            }
+      }
+    }
+    if (q.lcoriolis && q.Omega2 != 0.0) { dvp[0] += q.Omega2 * vp[1]; dvp[1] -= q.Omega2 * vp[0]; }   // dvvp_dt :3226-3233
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      dfp[(size_t)j * M + k] += vp[j];                              // dxxp_dt :3155-3161
+      dfp[(size_t)(3 + j) * M + k] += dvp[j];
+    }
+  }
+  if (ldt && q.ldt_adv) {
+    for (int o = 16; o > 0; o >>= 1) v_adv = fmax(v_adv, __shfl_xor_sync(0xffffffffu, v_adv, o));
+    if ((threadIdx.x & 31) == 0 && v_adv > 0.0) atomic_max_nonneg(dt1, v_adv);
+  }
+}
+
+// dt1_drag = (max_k tausp1 + sum_k mp_vcell*rho1*tausp1)/cdtp_drag per cell with particles
+// (particles_dust.f90:4843-4847, 4901-4910); constant tausp => the sum is np * (...)
+__global__ void part_dt_cells(PartPar q, const double *__restrict__ f, const int *__restrict__ np_i, double *__restrict__ dt1)
+{
+  const DevPar &c = c_par;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y, n = blockIdx.z;
+  double d = 0.0;
+  if (l < c.nx) {
+    const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+    const int npc = np_i[i];
+    if (npc > 0) {
+      d = q.tausp1;
+      if (q.ldrag_gas) d += npc * (q.rhop_swarm * exp(-f[(long long)q.ilnrho * c.mw + i]) * q.tausp1);
+      d /= q.cdtp_drag;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) d = fmax(d, __shfl_xor_sync(0xffffffffu, d, o));
+  if ((threadIdx.x & 31) == 0 && d > 0.0) atomic_max_nonneg(dt1, d);
+}
+
+// w_u += dfu ; f_out_u += beta*dt*dfu  (the deposit is part of df before the 2N update,
+// equ.f90:1046 + timestep.f90:162); f_out == nullptr when the update is done by axpy_update
+__global__ void part_backreact(int iux, const double *__restrict__ dfu, double *__restrict__ w, double *__restrict__ f_out,
+                               const double *__restrict__ dt_dev, double beta)
+{
+  const DevPar &c = c_par;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y;
+  const int n = blockIdx.z % c.nz, j = blockIdx.z / c.nz;
+  if (l >= c.nx) return;
+  const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+  const double v = dfu[(long long)j * c.mw + i];
+  const long long o = (long long)(iux + j) * c.mw + i;
+  w[o] += v;
+  if (f_out) f_out[o] += (beta * dt_dev[0]) * v;
+}
+
+__global__ void part_second(double *__restrict__ fp, const double *__restrict__ dfp, int npar, int mpar,
+                            const double *__restrict__ dt_dev, double beta)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= npar) return;
+  const double dtb = dt_dev[0] * beta;
+#pragma unroll
+  for (int j = 0; j < 6; j++) fp[(size_t)j * mpar + k] = fp[(size_t)j * mpar + k] + dtb * dfp[(size_t)j * mpar + k];
+}
+
+// aux fields for the host: np as doubles, rhop scaled by rhop_swarm (particles_map.f90:1733-1737)
+__global__ void part_aux_out(long long mw, const int *__restrict__ np_i, const double *__restrict__ rhop, double rhop_swarm,
+                             double *__restrict__ np_out, double *__restrict__ rhop_out)
+{
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= mw) return;
+  np_out[i] = (double)np_i[i];
+  rhop_out[i] = rhop_swarm * rhop[i];
+}

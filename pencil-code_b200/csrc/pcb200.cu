@@ -6,6 +6,8 @@
 //   -> (substep 1 with ldt) max-reduction -> dt -> streaming update.
 // No CPU fallback: every entry point fails loudly without a CUDA device.
 #include "kernels.cuh"
+#include "particles.cuh"
+#include <cub/device/device_radix_sort.cuh>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -13,6 +15,7 @@
 #include <dlfcn.h>
 #include <string>
 #include <vector>
+#include <algorithm>
 
 // ---- minimal NCCL declarations (resolved with dlopen so that single-GPU use
 // ---- does not need libnccl; same ABI as nccl.h 2.x) -----------------------
@@ -64,6 +67,19 @@ struct Ctx {
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
   // multi-GPU
   NcclApi nccl; ncclComm_t comm = nullptr; int rank = 0, nranks = 1;
+  // dust particles (particles.cuh)
+  struct Part {
+    bool on = false;
+    pcb200_particle_params pp;
+    PartPar q;
+    int cur = 0, nimn = 0, key_bits = 1;
+    double *fp[2] = {nullptr, nullptr}, *dfp[2] = {nullptr, nullptr};
+    int *ipar[2] = {nullptr, nullptr}, *inear[2] = {nullptr, nullptr};
+    unsigned *keys[2] = {nullptr, nullptr}, *vals[2] = {nullptr, nullptr};
+    int *imn_array = nullptr, *k1 = nullptr, *k2 = nullptr, *np_i = nullptr;
+    double *rhop = nullptr, *dfu = nullptr, *dt1 = nullptr;
+    void *cub_tmp = nullptr; size_t cub_bytes = 0;
+  } part;
   double *face[4] = {nullptr, nullptr, nullptr, nullptr};   // send lo/hi, recv lo/hi for the packed x,y faces
   size_t face_elems = 0;
   std::string err;
@@ -108,6 +124,7 @@ extern "C" int pcb200_init(int local_rank)
   return PCB200_OK;
 }
 
+static void part_free();
 static void free_fields()
 {
   for (int i = 0; i < 2; i++) { if (g.f[i]) cudaFree(g.f[i]); g.f[i] = nullptr; }
@@ -163,6 +180,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   if (P.ipx + P.nprocx * (P.ipy + P.nprocy * P.ipz) != g.rank || P.ipx < 0 || P.ipx >= P.nprocx || P.ipy < 0 || P.ipy >= P.nprocy)
     return fail(PCB200_EARG, "ipx,ipy,ipz do not match this rank (iproc = ipx + nprocx*(ipy + nprocy*ipz))");
   CK(cudaSetDevice(g.dev));
+  part_free();          // particle buffers depend on the grid: pcb200_particles_initialize must follow
   const bool realloc = !g.have_par || g.P.nx != P.nx || g.P.ny != P.ny || g.P.nz != P.nz || g.P.mvar != P.mvar;
   g.P = P;
   DevPar &h = g.hp;
@@ -480,6 +498,183 @@ static int launch_rhs(int auxm, const SubstepArgs &a, int z_lo, int z_hi, size_t
   return launch_rhs_t<2>(a, z_lo, z_hi, part_off, nb);
 }
 
+// ------------------------------------------------------------------------
+// dust particles
+static void part_free()
+{
+  Ctx::Part &p = g.part;
+  for (int i = 0; i < 2; i++) {
+    if (p.fp[i]) cudaFree(p.fp[i]); if (p.dfp[i]) cudaFree(p.dfp[i]); if (p.ipar[i]) cudaFree(p.ipar[i]);
+    if (p.inear[i]) cudaFree(p.inear[i]); if (p.keys[i]) cudaFree(p.keys[i]); if (p.vals[i]) cudaFree(p.vals[i]);
+    p.fp[i] = p.dfp[i] = nullptr; p.ipar[i] = p.inear[i] = nullptr; p.keys[i] = p.vals[i] = nullptr;
+  }
+  if (p.imn_array) cudaFree(p.imn_array); if (p.k1) cudaFree(p.k1); if (p.k2) cudaFree(p.k2); if (p.np_i) cudaFree(p.np_i);
+  if (p.rhop) cudaFree(p.rhop); if (p.dfu) cudaFree(p.dfu); if (p.dt1) cudaFree(p.dt1); if (p.cub_tmp) cudaFree(p.cub_tmp);
+  p.imn_array = p.k1 = p.k2 = p.np_i = nullptr; p.rhop = p.dfu = p.dt1 = nullptr; p.cub_tmp = nullptr; p.cub_bytes = 0;
+  p.on = false;
+}
+
+// pencil order of the mn-loop (setup_mm_nn, general.f90:230-335): imn_array[(n-n1)*ny+(m-m1)], 1-based
+static void host_imn_array(const pcb200_params &P, std::vector<int> &a)
+{
+  const int ny = P.ny, nz = P.nz, ncpus = P.nprocx * P.nprocy * P.nprocz;
+  a.assign((size_t)ny * nz, 0);
+  const int m1 = NG + 1, m2 = NG + ny, n1 = NG + 1, n2 = NG + nz;
+  const int m1i = m1 + NG - 1, m2i = m2 - NG + 1, n1i = n1 + NG - 1, n2i = n2 - NG + 1;
+  int imn = 1;
+  auto visit = [&](int m, int n) { int &v = a[(size_t)(n - n1) * ny + (m - m1)]; if (v == 0) v = imn++; };
+  if (ncpus == 1) { for (int n = n1; n <= n2; n++) for (int m = m1; m <= m2; m++) visit(m, n); return; }
+  for (int n = n1i + 2; n <= n2i - 2; n++) for (int m = m1i + 2; m <= m2i - 2; m++) visit(m, n);
+  for (int n = std::max(n2i - 1, n1 + 1); n <= n2; n++) for (int m = m1i + 2; m <= m2i - 2; m++) visit(m, n);
+  for (int n = n1; n <= std::min(n1i + 1, n2); n++) for (int m = m1i + 2; m <= m2i - 2; m++) visit(m, n);
+  const int lo = std::min(m1i + 1, m2), hi = std::max(m2i - 1, lo + 1);
+  for (int n = n1; n <= n2; n++) { for (int m = m1; m <= lo; m++) visit(m, n); for (int m = hi; m <= m2; m++) visit(m, n); }
+}
+
+extern "C" int pcb200_particles_initialize(const pcb200_particle_params *pp)
+{
+  if (!g.have_par) return fail(PCB200_ESTATE, "pcb200_particles_initialize before pcb200_initialize");
+  if (!pp) return fail(PCB200_EARG, "null particle parameters");
+  if (pp->abi_version != PCB200_ABI_VERSION) return fail(PCB200_EARG, "pcb200_particle_params.abi_version mismatch");
+  CK(cudaSetDevice(g.dev));
+  part_free();
+  if (pp->npar_loc <= 0) return PCB200_OK;
+  if (pp->mpar_loc < pp->npar_loc) return fail(PCB200_EARG, "mpar_loc < npar_loc");
+  if (g.nranks > 1) return fail(PCB200_EUNSUPP, "particles: migration/fold between ranks is not implemented (single rank only)");
+  if (pp->ldragforce_dust_par && pp->tausp <= 0.0) return fail(PCB200_EARG, "particles: tausp must be > 0");
+  const pcb200_params &P = g.P; const DevPar &h = g.hp;
+  Ctx::Part &p = g.part;
+  p.pp = *pp;
+  PartPar &q = p.q; memset(&q, 0, sizeof(q));
+  q.npar = pp->npar_loc; q.mpar = pp->mpar_loc;
+  q.ldrag_dust = pp->ldragforce_dust_par; q.ldrag_gas = pp->ldragforce_gas_par && pp->ldragforce_dust_par;
+  q.lcoriolis = pp->lcoriolis_force_par; q.ldt_adv = pp->ldt_adv_par;
+  const int np[3] = {P.nprocx, P.nprocy, P.nprocz}, nloc[3] = {P.nx, P.ny, P.nz}, ip[3] = {P.ipx, P.ipy, P.ipz};
+  const double hh[3] = {P.dx, P.dy, P.dz}, x0l[3] = {P.x0_loc, P.y0_loc, P.z0_loc};
+  for (int a = 0; a < 3; a++) {
+    q.wrap[a] = np[a] == 1;            // fold_df/fold_f nproc==1 branches (ghostfold_mpicomm.f90:46,86,120)
+    q.lperi[a] = 1;                    // bcpx=bcpy=bcpz='p' (particles_cdata defaults)
+    q.shift[a] = nloc[a] * ip[a];
+    q.xyz0[a] = P.xyz0[a]; q.Lxyz[a] = P.Lxyz[a]; q.h[a] = hh[a]; q.h_1[a] = 1.0 / hh[a]; q.x0_loc[a] = x0l[a];
+  }
+  // the index-space formula needs the gas grid's periodicity flag (grid.f90:2330-2334)
+  for (int a = 0; a < 3; a++) q.lperi[a] = P.lperi[a] ? 1 : 0;
+  q.h_1[0] = P.dx_1; q.h_1[1] = P.dy_1; q.h_1[2] = P.dz_1;
+  q.tausp1 = pp->tausp > 0.0 ? 1.0 / pp->tausp : 0.0;
+  q.rhop_swarm = pp->rhop_swarm; q.cdtp = pp->cdtp; q.cdtp_drag = pp->cdtp_drag; q.Omega2 = 2.0 * P.Omega;
+  q.iux = P.iux - 1; q.ilnrho = P.ilnrho - 1;
+  const size_t M = (size_t)pp->mpar_loc;
+  for (int i = 0; i < 2; i++) {
+    CK(cudaMalloc(&p.fp[i], 6 * M * sizeof(double))); CK(cudaMalloc(&p.dfp[i], 6 * M * sizeof(double)));
+    CK(cudaMalloc(&p.ipar[i], M * sizeof(int))); CK(cudaMalloc(&p.inear[i], 3 * M * sizeof(int)));
+    CK(cudaMalloc(&p.keys[i], M * sizeof(unsigned))); CK(cudaMalloc(&p.vals[i], M * sizeof(unsigned)));
+    CK(cudaMemsetAsync(p.dfp[i], 0, 6 * M * sizeof(double), g.st));
+  }
+  p.nimn = P.ny * P.nz;
+  p.key_bits = 1; while ((1 << p.key_bits) < p.nimn) p.key_bits++;
+  std::vector<int> imn; host_imn_array(P, imn);
+  CK(cudaMalloc(&p.imn_array, imn.size() * sizeof(int)));
+  CK(cudaMemcpyAsync(p.imn_array, imn.data(), imn.size() * sizeof(int), cudaMemcpyHostToDevice, g.st));
+  CK(cudaMalloc(&p.k1, p.nimn * sizeof(int))); CK(cudaMalloc(&p.k2, p.nimn * sizeof(int)));
+  CK(cudaMalloc(&p.np_i, (size_t)h.mw * sizeof(int))); CK(cudaMalloc(&p.rhop, (size_t)h.mw * sizeof(double)));
+  CK(cudaMalloc(&p.dfu, (size_t)3 * h.mw * sizeof(double))); CK(cudaMalloc(&p.dt1, sizeof(double)));
+  CK(cudaMemsetAsync(p.np_i, 0, (size_t)h.mw * sizeof(int), g.st));
+  CK(cudaMemsetAsync(p.rhop, 0, (size_t)h.mw * sizeof(double), g.st));
+  CK(cudaMemsetAsync(p.k1, 0, p.nimn * sizeof(int), g.st)); CK(cudaMemsetAsync(p.k2, 0, p.nimn * sizeof(int), g.st));
+  p.cub_bytes = 0;
+  CK(cub::DeviceRadixSort::SortPairs(nullptr, p.cub_bytes, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.npar, 0, p.key_bits, g.st));
+  CK(cudaMalloc(&p.cub_tmp, p.cub_bytes ? p.cub_bytes : 16));
+  CK(cudaStreamSynchronize(g.st));
+  p.cur = 0; p.on = true;
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_particles_load(const double *fp, const int32_t *ipar)
+{
+  Ctx::Part &p = g.part;
+  if (!p.on) return fail(PCB200_ESTATE, "pcb200_particles_load: particles are not initialised");
+  if (!fp || !ipar) return fail(PCB200_EARG, "null particle arrays");
+  const size_t M = (size_t)p.q.mpar;
+  CK(cudaMemcpyAsync(p.fp[p.cur], fp, 6 * M * sizeof(double), cudaMemcpyHostToDevice, g.st));
+  CK(cudaMemcpyAsync(p.ipar[p.cur], ipar, M * sizeof(int), cudaMemcpyHostToDevice, g.st));
+  CK(cudaMemsetAsync(p.dfp[p.cur], 0, 6 * M * sizeof(double), g.st));
+  CK(cudaStreamSynchronize(g.st));
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_particles_store(double *fp, double *dfp, int32_t *ipar, int32_t *ineargrid, int32_t *k1_imn, int32_t *k2_imn)
+{
+  Ctx::Part &p = g.part;
+  if (!p.on) return fail(PCB200_ESTATE, "pcb200_particles_store: particles are not initialised");
+  const size_t M = (size_t)p.q.mpar;
+  if (fp) CK(cudaMemcpyAsync(fp, p.fp[p.cur], 6 * M * sizeof(double), cudaMemcpyDeviceToHost, g.st));
+  if (dfp) CK(cudaMemcpyAsync(dfp, p.dfp[p.cur], 6 * M * sizeof(double), cudaMemcpyDeviceToHost, g.st));
+  if (ipar) CK(cudaMemcpyAsync(ipar, p.ipar[p.cur], M * sizeof(int), cudaMemcpyDeviceToHost, g.st));
+  if (ineargrid) CK(cudaMemcpyAsync(ineargrid, p.inear[p.cur], 3 * M * sizeof(int), cudaMemcpyDeviceToHost, g.st));
+  if (k1_imn) CK(cudaMemcpyAsync(k1_imn, p.k1, p.nimn * sizeof(int), cudaMemcpyDeviceToHost, g.st));
+  if (k2_imn) CK(cudaMemcpyAsync(k2_imn, p.k2, p.nimn * sizeof(int), cudaMemcpyDeviceToHost, g.st));
+  CK(cudaStreamSynchronize(g.st));
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_particles_get_aux(double *np, double *rhop)
+{
+  Ctx::Part &p = g.part;
+  if (!p.on) return fail(PCB200_ESTATE, "pcb200_particles_get_aux: particles are not initialised");
+  if (!np || !rhop) return fail(PCB200_EARG, "null aux arrays");
+  const long long mw = g.hp.mw;
+  double *tmp = p.dfu;      // scratch between substeps: dfu is rebuilt by every substep
+  part_aux_out<<<(unsigned)((mw + 255) / 256), 256, 0, g.st>>>(mw, p.np_i, p.rhop, p.q.rhop_swarm, tmp, tmp + mw);
+  g.launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(np, tmp, mw * sizeof(double), cudaMemcpyDeviceToHost, g.st));
+  CK(cudaMemcpyAsync(rhop, tmp + mw, mw * sizeof(double), cudaMemcpyDeviceToHost, g.st));
+  CK(cudaStreamSynchronize(g.st));
+  return PCB200_OK;
+}
+
+// particles_timestep_first + particles_boundconds (timestep.f90:127, equ.f90:169)
+static int part_before_rhs(int isub)
+{
+  Ctx::Part &p = g.part; const PartPar &q = p.q; const DevPar &h = g.hp;
+  const unsigned nb = (unsigned)((q.npar + 255) / 256);
+  part_first<<<nb, 256, 0, g.st>>>(p.dfp[p.cur], q.npar, q.mpar, isub == 1 ? 0.0 : g.P.alpha_ts[isub - 1]);
+  part_bc_map<<<nb, 256, 0, g.st>>>(q, p.fp[p.cur], p.inear[p.cur], p.imn_array, p.keys[0], p.vals[0]);
+  g.launches += 2;
+  CK(cudaGetLastError());
+  size_t bytes = p.cub_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(p.cub_tmp, bytes, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.npar, 0, p.key_bits, g.st));
+  const int nx = 1 - p.cur;
+  part_gather<<<nb, 256, 0, g.st>>>(q.npar, q.mpar, p.vals[1], p.fp[p.cur], p.fp[nx], p.dfp[p.cur], p.dfp[nx],
+                                    p.ipar[p.cur], p.ipar[nx], p.inear[p.cur], p.inear[nx]);
+  p.cur = nx;
+  CK(cudaMemsetAsync(p.k1, 0, p.nimn * sizeof(int), g.st)); CK(cudaMemsetAsync(p.k2, 0, p.nimn * sizeof(int), g.st));
+  part_pencil_bounds<<<nb, 256, 0, g.st>>>(q.npar, p.keys[1], p.k1, p.k2);
+  CK(cudaMemsetAsync(p.np_i, 0, (size_t)h.mw * sizeof(int), g.st));
+  CK(cudaMemsetAsync(p.rhop, 0, (size_t)h.mw * sizeof(double), g.st));
+  part_map_xxp<<<nb, 256, 0, g.st>>>(q, p.fp[p.cur], p.inear[p.cur], p.np_i, p.rhop);
+  g.launches += 3;
+  CK(cudaGetLastError());
+  return PCB200_OK;
+}
+
+// the particle share of the mn-loop (equ.f90:1046) + dxxp_dt/dvvp_dt (:379-382): needs valid ghost zones
+static int part_pencils(const double *fin, int ldt)
+{
+  Ctx::Part &p = g.part; const PartPar &q = p.q; const DevPar &h = g.hp; const pcb200_params &P = g.P;
+  CK(cudaMemsetAsync(p.dfu, 0, (size_t)3 * h.mw * sizeof(double), g.st));
+  if (ldt) CK(cudaMemsetAsync(p.dt1, 0, sizeof(double), g.st));
+  part_drag<<<(unsigned)((q.npar + 127) / 128), 128, 0, g.st>>>(q, fin, p.fp[p.cur], p.dfp[p.cur], p.inear[p.cur], p.dfu, p.dt1, ldt);
+  g.launches++;
+  if (ldt && q.ldrag_dust) {
+    dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
+    part_dt_cells<<<grd, blk, 0, g.st>>>(q, fin, p.np_i, p.dt1);
+    g.launches++;
+  }
+  CK(cudaGetLastError());
+  return PCB200_OK;
+}
+
 static int do_substep(int isub, int ldiagnos)
 {
   const pcb200_params &P = g.P;
@@ -489,6 +684,7 @@ static int do_substep(int isub, int ldiagnos)
   // boundcond.f90:1283-1290), each over the full extent of the other axes.  Per axis: wrap
   // locally / physical boundary condition / exchange with the neighbour ranks.  Consecutive
   // locally periodic axes share one launch.  Only the z exchange overlaps with compute.
+  if (g.part.on) if ((rc = part_before_rhs(isub))) return rc;
   const int np[3] = {P.nprocx, P.nprocy, P.nprocz};
   bool pend[3] = {false, false, false};
   auto flush = [&]() -> int {
@@ -532,6 +728,10 @@ static int do_substep(int isub, int ldiagnos)
   a.write_w = isub < 3;
   a.write_f = need_dt ? 0 : 1;
   if (need_dt) a.write_w = 1;
+  if (g.part.on) {
+    if (multi) { CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0)); }
+    if ((rc = part_pencils(fin, need_dt))) return rc;
+  }
   int nb0 = 0, nb1 = 0, nb2 = 0;
   if (!multi) {
     if ((rc = launch_rhs(auxm, a, 0, P.nz, 0, &nb0))) return rc;
@@ -542,6 +742,14 @@ static int do_substep(int isub, int ldiagnos)
     if ((rc = launch_rhs(auxm, a, 0, NG, nb0, &nb1))) return rc;
     if ((rc = launch_rhs(auxm, a, P.nz - NG, P.nz, (size_t)nb0 + nb1, &nb2))) return rc;
   }
+  if (g.part.on && g.part.q.ldrag_gas) {
+    // the deposited drag is part of df (equ.f90:1046): add it to the 2N register and, when this
+    // launch already produced the new state, to f_out as well (otherwise axpy_update does)
+    dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz * 3);
+    part_backreact<<<grd, blk, 0, g.st>>>(P.iux - 1, g.part.dfu, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
+    g.launches++;
+    CK(cudaGetLastError());
+  }
   if (auxm > 0) {
     reduce_partials<<<1, NRED * 32, 0, g.st>>>(g.partials, nb0 + nb1 + nb2, g.red_dev);
     g.launches++;
@@ -549,7 +757,7 @@ static int do_substep(int isub, int ldiagnos)
   }
   if (need_dt) {
     const double floor1 = P.dtmax != 0.0 ? 1.0 / P.dtmax : 0.0;
-    finish_dt<<<1, 32, 0, g.st>>>(g.red_dev, floor1, g.dt_dev);
+    finish_dt<<<1, 32, 0, g.st>>>(g.red_dev, floor1, g.dt_dev, g.part.on ? g.part.dt1 : nullptr);
     g.launches++;
     if (g.nranks > 1) {
       NK(g.nccl.AllReduce(g.dt_dev + 1, g.dt_dev + 1, 1, 8, 2 /*ncclMax*/, g.comm, g.st));     // set_dt, sub.f90:3909
@@ -558,6 +766,12 @@ static int do_substep(int isub, int ldiagnos)
     }
     dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz * P.mvar);
     axpy_update<<<grd, blk, 0, g.st>>>(fin, g.w, fout, g.dt_dev, P.beta_ts[0]);
+    g.launches++;
+    CK(cudaGetLastError());
+  }
+  if (g.part.on) {
+    part_second<<<(unsigned)((g.part.q.npar + 255) / 256), 256, 0, g.st>>>(g.part.fp[g.part.cur], g.part.dfp[g.part.cur],
+                                                                         g.part.q.npar, g.part.q.mpar, g.dt_dev, P.beta_ts[isub - 1]);
     g.launches++;
     CK(cudaGetLastError());
   }
@@ -677,6 +891,7 @@ extern "C" int pcb200_finalize(void)
   for (int q = 0; q < PCB200_NPROF; q++) { if (g.zprof[q]) cudaFree(g.zprof[q]); g.zprof[q] = nullptr; }
   for (int i = 0; i < 4; i++) { if (g.face[i]) cudaFree(g.face[i]); g.face[i] = nullptr; }
   g.face_elems = 0;
+  part_free();
   if (g.comm && g.nccl.CommDestroy) { g.nccl.CommDestroy(g.comm); g.comm = nullptr; }
   g.have_par = false; g.npartials = 0; g.nranks = 1; g.rank = 0;
   return PCB200_OK;

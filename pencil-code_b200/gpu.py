@@ -139,3 +139,17 @@ class GPU:
         n = C.c_int()
         self._ck(self.lib.pcb200_rhs_kernel_time(C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    # -- dust particles (called by the wrapper when lparticles) --------
+    def particles_initialize(self, pp):
+        self._ck(self.lib.pcb200_particles_initialize(C.byref(pp)))
+
+    def particles_load(self, st):
+        """st: setups.ParticleState (fp[6][mpar], ipar[mpar])."""
+        self._ck(self.lib.pcb200_particles_load(st.fp.ctypes.data, st.ipar.ctypes.data))
+
+    def particles_store(self, st):
+        self._ck(self.lib.pcb200_particles_store(st.fp.ctypes.data, st.dfp.ctypes.data, st.ipar.ctypes.data,
+                                                 st.ineargrid.ctypes.data, st.k1_imn.ctypes.data, st.k2_imn.ctypes.data))
+        self._ck(self.lib.pcb200_particles_get_aux(st.np_.ctypes.data, st.rhop.ctypes.data))
+        return st

