@@ -142,6 +142,8 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--particles", type=int, default=0,
+                    help="dust particles per GPU (BASELINE config 5 is 256^3 cells + 1.25e7 particles per GPU); N=1 only")
     ap.add_argument("--decomp", default="", help="nprocx,nprocy,nprocz (default: z-slabs 1,1,N)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -179,6 +181,11 @@ def main():
     dev.initialize_GPU(P, zprof)
     dev.register_GPU(f)
     dev.load_farray()
+    if args.particles:
+        pp = pk.setups.make_particle_params(P, args.particles, tausp=0.1, eps_dtog=0.5)
+        pst = pk.setups.synthetic_particles(P, pp)
+        dev.particles_initialize(pp)
+        dev.particles_load(pst)
 
     def barrier():
         dev.sync()
@@ -253,7 +260,7 @@ def main():
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"isothermal helical-MHD box (BASELINE config 3), {n}^3 cells per GPU, mvar=7",
                    "global_grid": [n * nproc[0], n * nproc[1], n * nproc[2]], "decomposition": list(nproc), "step": "one RK3 time step = 3 substeps incl. BCs, CFL dt, 2N update",
-                   "l2": f"inputs larger than L2 ({f.nbytes / 1e9:.2f} GB per buffer)", "dt": dt},
+                   "particles_per_gpu": args.particles, "l2": f"inputs larger than L2 ({f.nbytes / 1e9:.2f} GB per buffer)", "dt": dt},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if ach else None,
                      "traffic": traffic, "peak_source": peak_src, "kernel": "rhs_tma<MAG=1,ENT=0>", "launches_timed": kcount,
                      "avg_launch_ms": kms, "kernel_ms_per_substep": ksub, "algorithmic_bytes_per_cell": b_alg,

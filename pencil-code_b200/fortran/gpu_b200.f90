@@ -65,6 +65,16 @@ module GPU
     real(c_double) :: reserved_d(8)
   endtype pcb200_params
 !
+  type, bind(C) :: pcb200_particle_params
+    integer(c_int32_t) :: abi_version
+    integer(c_int32_t) :: npar_loc, mpar_loc
+    integer(c_int32_t) :: ldragforce_dust_par, ldragforce_gas_par, lcoriolis_force_par
+    integer(c_int32_t) :: ldt_adv_par, lcheck_exact_frontier
+    integer(c_int32_t) :: reserved_i(8)
+    real(c_double) :: tausp, rhop_swarm, cdtp, cdtp_drag
+    real(c_double) :: reserved_d(8)
+  endtype pcb200_particle_params
+!
   type, bind(C) :: pcb200_forcing
     real(c_double) :: coef1(3), coef2(3), fda(3), kk(3)
     real(c_double) :: phase, fact
@@ -114,6 +124,24 @@ module GPU
       import :: c_int, c_char
       character(kind=c_char), dimension(128), intent(in) :: id
       integer(c_int), value :: rank, nranks
+    endfunction
+    integer(c_int) function pcb200_particles_initialize(pp) bind(C,name='pcb200_particles_initialize')
+      import :: c_int, pcb200_particle_params
+      type(pcb200_particle_params), intent(in) :: pp
+    endfunction
+    integer(c_int) function pcb200_particles_load(fp,ipar) bind(C,name='pcb200_particles_load')
+      import :: c_int, c_double, c_int32_t
+      real(c_double), dimension(*), intent(in) :: fp
+      integer(c_int32_t), dimension(*), intent(in) :: ipar
+    endfunction
+    integer(c_int) function pcb200_particles_store(fp,dfp,ipar,ineargrid,k1_imn,k2_imn) bind(C,name='pcb200_particles_store')
+      import :: c_int, c_double, c_int32_t
+      real(c_double), dimension(*) :: fp, dfp
+      integer(c_int32_t), dimension(*) :: ipar, ineargrid, k1_imn, k2_imn
+    endfunction
+    integer(c_int) function pcb200_particles_get_aux(np,rhop) bind(C,name='pcb200_particles_get_aux')
+      import :: c_int, c_double
+      real(c_double), dimension(*) :: np, rhop
     endfunction
     integer(c_int) function pcb200_finalize() bind(C,name='pcb200_finalize')
       import :: c_int
@@ -247,7 +275,9 @@ contains
       if (lselfgravity) str=trim(str)//', '//'selfgravity'
       if (lsolid_cells) str=trim(str)//', '//'solid_cells'
       if (lspecial) str=trim(str)//', '//'special'
-      if (lparticles) str=trim(str)//', '//'particles'
+      if (lparticles .and. ncpus>1) str=trim(str)//', '//'particles on more than one rank'
+      if (lparticles_radius.or.lparticles_number.or.lparticles_density.or.lparticles_sink.or. &
+          lparticles_selfgravity.or.lparticles_blocks) str=trim(str)//', '//'particle sub-modules'
       if (.not.lcartesian_coords) str=trim(str)//', '//'curvilinear coordinates'
       if (.not.all(lequidist)) str=trim(str)//', '//'non-equidistant grid'
       if (itorder/=3) str=trim(str)//', '//'itorder/=3'
@@ -314,9 +344,37 @@ contains
         prof=exp(-0.5*((xyz0(3)+Lxyz(3)-z(n1:n2))/wcool)**2)
         call check(pcb200_set_zprofile(2_c_int,prof,int(nz,c_int)),'initialize_GPU')
       endif
+      if (lparticles) call initialize_particles_GPU
       lvery_first=.true.      ! force a full upload after RELOAD / rsnap
 !
     endsubroutine initialize_GPU
+!***********************************************************************
+    subroutine initialize_particles_GPU
+!
+!  particles_dust run parameters the device needs (particles_dust.f90:59-123,
+!  particles_cdata.f90): constant friction time, TSC particle-mesh scheme.
+!
+      use Particles_cdata
+      use Particles, only: tausp, cdtp, cdtp_drag, ldragforce_dust_par, ldragforce_gas_par, &
+                           lcoriolis_force_par, ldt_adv_par
+!
+      type(pcb200_particle_params) :: pp
+!
+      if (.not.lparticlemesh_tsc .or. .not.linterpolate_spline) &
+          call fatal_error('initialize_GPU','particles on the GPU need lparticlemesh_tsc=T, linterpolate_spline=T')
+      pp%abi_version=PCB200_ABI_VERSION
+      pp%npar_loc=npar_loc; pp%mpar_loc=mpar_loc
+      pp%ldragforce_dust_par=merge(1,0,ldragforce_dust_par)
+      pp%ldragforce_gas_par=merge(1,0,ldragforce_gas_par)
+      pp%lcoriolis_force_par=merge(1,0,lcoriolis_force_par)
+      pp%ldt_adv_par=merge(1,0,ldt_adv_par)
+      pp%lcheck_exact_frontier=merge(1,0,lcheck_exact_frontier)
+      pp%reserved_i=0
+      pp%tausp=tausp; pp%rhop_swarm=rhop_swarm; pp%cdtp=cdtp; pp%cdtp_drag=cdtp_drag
+      pp%reserved_d=0.
+      call check(pcb200_particles_initialize(pp),'initialize_particles_GPU')
+!
+    endsubroutine initialize_particles_GPU
 !***********************************************************************
     subroutine register_GPU(f)
 !
@@ -342,6 +400,7 @@ contains
 !  cdata:dt and t (timestep.f90:152-190) stay right.
 !
       use Forcing, only: forcing_pars_hel
+      use Particles_cdata, only: fp, ipar
 !
       real, dimension (mx,my,mz,mfarray), intent(INOUT) :: f
       integer,                            intent(IN)    :: isubstep
@@ -358,11 +417,17 @@ contains
         frc%coef1=coef1; frc%coef2=coef2; frc%fda=fda; frc%kk=kk; frc%phase=phase; frc%fact=fact
         call check(pcb200_set_forcing(frc),'rhs_GPU')
       endif
+!  particles travel with f: uploaded once, then owned by the device
+!  (the host skips particles_timestep_first/second and particles_boundconds when lgpu)
+      if (lparticles .and. lvery_first) call check(pcb200_particles_load(fp,ipar),'rhs_GPU')
       dtc=dt
       call check(pcb200_substep(int(isubstep,c_int),merge(1_c_int,0_c_int,lvery_first), &
                                 merge(1_c_int,0_c_int,early_finalize),merge(1_c_int,0_c_int,ldiagnos),dtc),'rhs_GPU')
       if (isubstep==1 .and. ldt) dt=dtc
-      if (isubstep==1 .and. ldiagnos) call check(pcb200_get_diagnostics(gpu_diag,16_c_int),'rhs_GPU')
+      if (isubstep==1 .and. ldiagnos) then
+        call check(pcb200_get_diagnostics(gpu_diag,16_c_int),'rhs_GPU')
+        call diagnostics_to_fname
+      endif
       lvery_first=.false.
       call keep_compiler_quiet(f)
 !
@@ -375,7 +440,65 @@ contains
       real, dimension (mx,my,mz,mfarray), intent(OUT) :: f
 !
       call check(pcb200_copy_farray(f),'copy_farray_from_GPU')
+      if (lparticles) call copy_particles_from_GPU(f)
 !
     endsubroutine copy_farray_from_GPU
+!***********************************************************************
+    subroutine copy_particles_from_GPU(f)
+!
+!  Particle state for wsnap/pvar.dat and the host diagnostics: fp, dfp, ipar,
+!  ineargrid, the pencil ranges k1_imn/k2_imn and the aux fields np, rhop.
+!
+      use Particles_cdata
+!
+      real, dimension (mx,my,mz,mfarray), intent(INOUT) :: f
+!
+      call check(pcb200_particles_store(fp,dfp,ipar,ineargrid,k1_imn,k2_imn),'copy_particles_from_GPU')
+      where (k1_imn/=0)
+        npar_imn=k2_imn-k1_imn+1
+      elsewhere
+        npar_imn=0
+      endwhere
+      if (inp/=0 .and. irhop/=0) call check(pcb200_particles_get_aux(f(:,:,:,inp),f(:,:,:,irhop)),'copy_particles_from_GPU')
+!
+    endsubroutine copy_particles_from_GPU
+!***********************************************************************
+    subroutine diagnostics_to_fname
+!
+!  0-D diagnostics computed on the device go straight into fname, so that
+!  print.in/time_series.dat work without the full D2H copy of equ.f90:344-347.
+!  The indices idiag_* are module-private; Hydro and Magnetic hand out their
+!  addresses through pushdiags2c (hydro.f90:8110, magnetic.f90:10657), which
+!  also sets the reduction type (sum->sqrt, max).  gpu_diag follows the
+!  PCB200_DIAG_* order of pcb200.h.
+!
+      use Hydro, only: hydro_diags => pushdiags2c
+      use Magnetic, only: magnetic_diags => pushdiags2c
+!
+      integer(KIND=ikind8), dimension(12) :: p_hyd
+      integer(KIND=ikind8), dimension(8) :: p_mag
+!
+      if (lhydro) then
+        call hydro_diags(p_hyd)
+        call put(p_hyd(1),gpu_diag(1))              ! idiag_urms: sum of u^2 (ilabel_sum_sqrt)
+        call put(p_hyd(5),sqrt(gpu_diag(2)))        ! idiag_umax (ilabel_max)
+      endif
+      if (lmagnetic) then
+        call magnetic_diags(p_mag)
+        call put(p_mag(1),gpu_diag(5))              ! idiag_brms: sum of b^2
+        call put(p_mag(2),sqrt(gpu_diag(6)))        ! idiag_bmax
+      endif
+!
+    contains
+      subroutine put(addr,val)
+        integer(KIND=ikind8), intent(in) :: addr
+        real(c_double), intent(in) :: val
+        type(c_ptr) :: cp
+        integer, pointer :: idiag
+        cp=transfer(addr,cp)
+        call c_f_pointer(cp,idiag)
+        if (idiag/=0) fname(idiag)=val
+      endsubroutine put
+    endsubroutine diagnostics_to_fname
 !***********************************************************************
 endmodule GPU
