@@ -264,7 +264,10 @@ def main():
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if ach else None,
                      "traffic": traffic, "peak_source": peak_src, "kernel": "rhs_tma<MAG=1,ENT=0>", "launches_timed": kcount,
                      "avg_launch_ms": kms, "kernel_ms_per_substep": ksub, "algorithmic_bytes_per_cell": b_alg,
-                     "step_frac": cells_local * b_alg * 3 / (ms / args.steps * 1e-3) / 1e9 / peak},
+                     "step_frac": cells_local * b_alg * 3 / (ms / args.steps * 1e-3) / 1e9 / peak,
+                     # with ldt the f write of substep 1 is done by axpy_update, not by this kernel:
+                     # its own share of the SURVEY 8d bytes is 9/10
+                     "frac_kernel_own_bytes": (0.9 * ach / peak) if ach else None},
         "clocks": clk, "gpu_launches": launches,
     }
     if e2e:
