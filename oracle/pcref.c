@@ -108,6 +108,36 @@ double pcref_derij(const double *f, int mx, int my, int l, int m, int n, int i, 
                 + 2. * (p[3 * sa + 3 * sb] - p[-3 * sa + 3 * sb] + p[-3 * sa - 3 * sb] - p[3 * sa - 3 * sb]));
 }
 
+/* derij_main, lbidiagonal_derij=F: "the old, straight-forward scheme", product of two
+ * 1-D 6th-order first-derivative stencils, 36 points (deriv.f90:1430-1557).  Inner
+ * differences along a (x for (x,y) and (z,x); y for (y,z)), outer along b. */
+double pcref_derij_full(const double *f, int mx, int my, int l, int m, int n, int i, int j,
+                        double di_1, double dj_1)
+{
+  const double *p = f + ((long)n * my + m) * mx + l;
+  const long sx = 1, sy = mx, sz = (long)mx * my;
+  long sa, sb;
+  double fac;
+  if (i + j == 3) { const double dx_1 = (i == 1) ? di_1 : dj_1, dy_1 = (i == 1) ? dj_1 : di_1;
+                    fac = (1. / (60. * 60.)) * dx_1 * dy_1; sa = sx; sb = sy; }
+  else if (i + j == 5) { const double dy_1 = (i == 2) ? di_1 : dj_1, dz_1 = (i == 2) ? dj_1 : di_1;
+                    fac = (1. / (60. * 60.)) * dy_1 * dz_1; sa = sy; sb = sz; }
+  else { const double dx_1 = (i == 1) ? di_1 : dj_1, dz_1 = (i == 1) ? dj_1 : di_1;
+                    fac = (1. / (60. * 60.)) * dz_1 * dx_1; sa = sx; sb = sz; }
+#define DROW(q) (45. * ((q)[sa] - (q)[-sa]) - 9. * ((q)[2 * sa] - (q)[-2 * sa]) + ((q)[3 * sa] - (q)[-3 * sa]))
+  return fac * (45. * (DROW(p + sb) - DROW(p - sb)) - 9. * (DROW(p + 2 * sb) - DROW(p - 2 * sb))
+                + (DROW(p + 3 * sb) - DROW(p - 3 * sb)));
+#undef DROW
+}
+
+void pcref_derij_full_field(const double *f, int nx, int ny, int nz, int i, int j,
+                            double di_1, double dj_1, double *out)
+{
+  const int mx = nx + 2 * NG, my = ny + 2 * NG;
+  for (int n = 0; n < nz; n++) for (int m = 0; m < ny; m++) for (int l = 0; l < nx; l++)
+    out[((long)n * ny + m) * nx + l] = pcref_derij_full(f, mx, my, l + NG, m + NG, n + NG, i, j, di_1, dj_1);
+}
+
 void pcref_der_field(const double *f, int nx, int ny, int nz, int j, double d_1, double *out)
 {
   const int mx = nx + 2 * NG, my = ny + 2 * NG;
@@ -249,7 +279,8 @@ static void rhs_point(const double *f, double *df, const pcb200_params *par,
 #define DER2(k, j) (d1[(j)-1] == 0. ? 0. : pcref_der2(FV(k), mx, my, l, m, n, (j), d1[(j)-1]))
 #define DER6U(k, j) (d1[(j)-1] == 0. ? 0. : pcref_der6_upwind(FV(k), mx, my, l, m, n, (j), d1[(j)-1]))
 #define DERIJ(k, i, j) ((d1[(i)-1] == 0. || d1[(j)-1] == 0.) ? 0. : \
-        pcref_derij(FV(k), mx, my, l, m, n, (i), (j), d1[(i)-1], d1[(j)-1]))
+        (par->lbidiagonal_derij ? pcref_derij(FV(k), mx, my, l, m, n, (i), (j), d1[(i)-1], d1[(j)-1]) \
+                                : pcref_derij_full(FV(k), mx, my, l, m, n, (i), (j), d1[(i)-1], d1[(j)-1])))
   const int iu = par->iux - 1, ilr = par->ilnrho - 1, is = par->iss - 1, ia = par->iax - 1;
 
   double maxadvec = 0., advec2 = 0., advec_cs2 = 0., maxdiffus = 0.;

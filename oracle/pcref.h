@@ -32,6 +32,13 @@ double pcref_der6_upwind(const double *f, int mx, int my, int l, int m, int n, i
 double pcref_derij(const double *f, int mx, int my, int l, int m, int n, int i, int j,
                    double di_1, double dj_1);
 
+/* lbidiagonal_derij=F: 36-point product stencil (deriv.f90:1430-1557) */
+double pcref_derij_full(const double *f, int mx, int my, int l, int m, int n, int i, int j,
+                        double di_1, double dj_1);
+
+void pcref_derij_full_field(const double *f, int nx, int ny, int nz, int i, int j,
+                            double di_1, double dj_1, double *out);
+
 /* whole-array versions used by the unit tests (interior only, out has nx*ny*nz) */
 void pcref_der_field (const double *f, int nx, int ny, int nz, int j, double d_1, double *out);
 void pcref_der2_field(const double *f, int nx, int ny, int nz, int j, double d_1, double *out);

@@ -30,6 +30,8 @@ class Oracle:
             getattr(L, name).restype = None
         L.pcref_derij_field.argtypes = [p, i, i, i, i, i, d, d, p]
         L.pcref_derij_field.restype = None
+        L.pcref_derij_full_field.argtypes = [p, i, i, i, i, i, d, d, p]
+        L.pcref_derij_full_field.restype = None
         L.pcref_boundconds.argtypes = [p, C.POINTER(abi.Params)]
         L.pcref_boundconds.restype = None
         L.pcref_rhs.argtypes = [p, p, C.POINTER(abi.Params), i, C.POINTER(d), p]
@@ -79,6 +81,11 @@ class Oracle:
     def derij(self, f, i, j, di_1, dj_1):
         nz, ny, nx = (s - 6 for s in f.shape)
         return self._field(self.lib.pcref_derij_field, f, nx, ny, nz, i, j, di_1, dj_1)
+
+    def derij_full(self, f, i, j, di_1, dj_1):
+        """lbidiagonal_derij=F (36-point product stencil)."""
+        mz, my, mx = f.shape
+        return self._field(self.lib.pcref_derij_full_field, f, mx - 6, my - 6, mz - 6, i, j, di_1, dj_1)
 
     def boundconds(self, f, par):
         self.lib.pcref_boundconds(f.ctypes.data, C.byref(par))

@@ -16,6 +16,7 @@ struct DevPar {
   int slot[NROLE];               // role -> storage slot, -1 = absent
   long long foff[NROLE];         // slot*mw: element offset of the role's variable
   int lupw_uu, lupw_lnrho, lupw_ss;
+  int lbidiag;                 // lbidiagonal_derij (cdata.f90:568)
   int iheatcond, lcooling, lviscosity_heat, lohmic_heat, lgravz, ldensity, lhydro;
   double dx_1, dy_1, dz_1;       // 0 for degenerate directions
   double dxyz_2;                 // grid.f90:2567-2570

@@ -98,6 +98,8 @@ __global__ void reduce_partials(const double *__restrict__ partials, int nblocks
 struct GlobalAcc {
   const double *p[NROLE];
   long long sy, sz;
+  bool bd;
+  PC_DEV bool bidiag() const { return bd; }
   template <int R> PC_DEV double c() const { return __ldg(p[R]); }
   template <int R, int K> PC_DEV double x() const { return __ldg(p[R] + K); }
   template <int R, int K> PC_DEV double y() const { return __ldg(p[R] + K * sy); }
@@ -137,7 +139,7 @@ __global__ void __launch_bounds__(256) rhs_global(SubstepArgs a)
   if (l < c.nx && m < c.ny && n < a.z_hi) {
     const long long idx = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
     GlobalAcc acc;
-    acc.sy = c.sy; acc.sz = c.sz;
+    acc.sy = c.sy; acc.sz = c.sz; acc.bd = c.lbidiag != 0;
 #pragma unroll
     for (int r = 0; r < NROLE; r++) acc.p[r] = c.slot[r] >= 0 ? a.f_in + (long long)c.slot[r] * c.mw + idx : a.f_in;
     double rhs[NROLE];
@@ -185,6 +187,7 @@ struct MarchAcc {
   unsigned sb[7];       // byte offset of this thread's cell in the ring slot of plane z+k, k=-3..3
   unsigned pb;          // byte offset of this thread's cell in the plain-field slot of plane z
   double w[NROLE][7];   // own column, planes z-3..z+3
+  PC_DEV constexpr bool bidiag() const { return true; }
   template <int R, int OFF> PC_DEV double cenv() const
   { return R < 6 ? lds_at(smem0, sb[3], (R * NSLOT) * PE + OFF) : lds_at(smem0, pb, ((R - 6) * 2) * PE + OFF); }
   template <int R> PC_DEV double c() const { return w[R][3]; }
@@ -587,8 +590,9 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, in
                ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar)) : "memory");
 }
 
-template <bool MAG, bool ENT>
+template <bool MAG, bool ENT, bool BD = true>
 struct TmaAcc {
+  PC_DEV constexpr bool bidiag() const { return BD; }
   const double *smem0;  // ring [ring role][NSLOT][PEP], then plain [plain role][2][PEP]
   unsigned sb[7];       // byte offset of this thread's cell in the ring slot of plane z+k, k=-3..3
   unsigned pb;          // byte offset of this thread's cell in the plain-field slot of plane z
@@ -611,7 +615,7 @@ template <bool MAG, bool ENT> struct TmaCfg {
   static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + 8 * NRED + 2) + 128;   // + reduction scratch + mbarrier + alignment slack
 };
 
-template <bool MAG, bool ENT, int AUXM, bool RW>
+template <bool MAG, bool ENT, int AUXM, bool RW, bool BD = true>
 __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_constant__ CUtensorMap tmap)
 {
   const DevPar &c = c_par;
@@ -663,7 +667,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
       tma_load_3d(plain + ((size_t)(r - 6) * 2) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + NG, full);
     }
   }
-  TmaAcc<MAG, ENT> acc;
+  TmaAcc<MAG, ENT, BD> acc;
   acc.smem0 = smem;
   double wnext[NROLE];
 #pragma unroll

@@ -169,7 +169,8 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   const pcb200_params &P = *par;
   // same policy as gpu_astaroth.f90:32-71: refuse what is not implemented
   if (!P.lhydro || !P.ldensity) return fail(PCB200_EUNSUPP, "No GPU implementation without hydro+density");
-  if (!P.lbidiagonal_derij) return fail(PCB200_EUNSUPP, "No GPU implementation for lbidiagonal_derij=F");
+  if (!P.lbidiagonal_derij && ((P.nx + 2 * NG) % 2 != 0 || g.use_cpasync))
+    return fail(PCB200_EUNSUPP, "lbidiagonal_derij=F needs the TMA kernel (even nx)");
   if (P.nx < 2 * NG || P.ny < 2 * NG || P.nz < 2 * NG) return fail(PCB200_EUNSUPP, "local grid smaller than 6 points per direction");
   if (P.mvar < 4 || P.mvar > PCB200_MAXVAR) return fail(PCB200_EARG, "mvar out of range");
   if (P.lentropy && !P.iss) return fail(PCB200_EARG, "lentropy without iss");
@@ -193,6 +194,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   if (P.lmagnetic) { h.slot[R_AX] = P.iax - 1; h.slot[R_AY] = P.iay - 1; h.slot[R_AZ] = P.iaz - 1; }
   for (int r = 0; r < NROLE; r++) if (h.slot[r] >= P.mvar) return fail(PCB200_EARG, "variable slot beyond mvar");
   for (int r = 0; r < NROLE; r++) h.foff[r] = h.slot[r] >= 0 ? (long long)h.slot[r] * h.mw : 0;
+  h.lbidiag = P.lbidiagonal_derij;
   h.lupw_uu = P.lupw_uu; h.lupw_lnrho = P.lupw_lnrho; h.lupw_ss = P.lupw_ss;
   h.iheatcond = P.iheatcond; h.lcooling = P.lcooling; h.lviscosity_heat = P.lviscosity_heat; h.lohmic_heat = P.lohmic_heat;
   h.lgravz = P.lgravz; h.ldensity = P.ldensity; h.lhydro = P.lhydro;
@@ -256,7 +258,8 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   OPTIN(false, true, 0);  OPTIN(false, true, 1);  OPTIN(false, true, 2);
   OPTIN(true, true, 0);   OPTIN(true, true, 1);   OPTIN(true, true, 2);
 #undef OPTIN
-#define OPTINT(M, E, A, R) CK(cudaFuncSetAttribute(rhs_tma<M, E, A, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TmaCfg<M, E>::SMEM))
+#define OPTINT(M, E, A, R) CK(cudaFuncSetAttribute(rhs_tma<M, E, A, R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TmaCfg<M, E>::SMEM)); \
+                           CK(cudaFuncSetAttribute(rhs_tma<M, E, A, R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TmaCfg<M, E>::SMEM))
 #define OPTINT4(M, E) OPTINT(M, E, 0, false); OPTINT(M, E, 1, false); OPTINT(M, E, 2, false); OPTINT(M, E, 0, true)
   OPTINT4(false, false); OPTINT4(true, false); OPTINT4(false, true); OPTINT4(true, true);
 #undef OPTINT4
@@ -473,8 +476,12 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
     const bool rw = a.alpha != 0.0;
     // the old 2N register is only read on substeps 2,3, which never need the reductions
-#define LT(M, E) do { if (rw) rhs_tma<M, E, 0, true><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); \
-                      else    rhs_tma<M, E, AUXM, false><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); } while (0)
+#define LT(M, E) do { if (P.lbidiagonal_derij) { \
+                        if (rw) rhs_tma<M, E, 0, true, true><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); \
+                        else    rhs_tma<M, E, AUXM, false, true><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); \
+                      } else { \
+                        if (rw) rhs_tma<M, E, 0, true, false><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); \
+                        else    rhs_tma<M, E, AUXM, false, false><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); } } while (0)
     if (M && E) LT(true, true); else if (M) LT(true, false); else if (E) LT(false, true); else LT(false, false);
 #undef LT
   } else {

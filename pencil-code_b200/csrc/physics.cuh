@@ -41,25 +41,38 @@ template <int R, class A> PC_DEV double d6y(const A &a, double f1)
 template <int R, class A> PC_DEV double d6z(const A &a, double f1)
 { return f1 * (-20.0 * a.template c<R>() + 15.0 * (a.template z<R, 1>() + a.template z<R, -1>()) - 6.0 * (a.template z<R, 2>() + a.template z<R, -2>()) + (a.template z<R, 3>() + a.template z<R, -3>())); }
 
-// bidiagonal mixed derivatives
+// mixed derivatives (derij_main, deriv.f90:1343-1580).  a.bidiag(): lbidiagonal_derij=T, the
+// 12-point scheme (:1385-1423); otherwise the 36-point product of two first-derivative
+// stencils (:1430-1557), inner differences along x (xy, zx) or y (yz), outer along y or z.
+// fij = d_i d_j/720 in both cases (the product stencil has 1/3600 = 0.2/720).
+#define PC_DROW(ACC, K2) (45.0 * (a.template ACC<R, 1, K2>() - a.template ACC<R, -1, K2>()) \
+                          - 9.0 * (a.template ACC<R, 2, K2>() - a.template ACC<R, -2, K2>()) \
+                          + (a.template ACC<R, 3, K2>() - a.template ACC<R, -3, K2>()))
+#define PC_DFULL(ACC) (0.2 * fij) * (45.0 * (PC_DROW(ACC, 1) - PC_DROW(ACC, -1)) - 9.0 * (PC_DROW(ACC, 2) - PC_DROW(ACC, -2)) \
+                                     + (PC_DROW(ACC, 3) - PC_DROW(ACC, -3)))
 template <int R, class A> PC_DEV double dxy(const A &a, double fij)
 {
+  if (!a.bidiag()) return PC_DFULL(xy);
   return fij * (270.0 * (a.template xy<R, 1, 1>() - a.template xy<R, -1, 1>() + a.template xy<R, -1, -1>() - a.template xy<R, 1, -1>())
                 - 27.0 * (a.template xy<R, 2, 2>() - a.template xy<R, -2, 2>() + a.template xy<R, -2, -2>() - a.template xy<R, 2, -2>())
                 + 2.0 * (a.template xy<R, 3, 3>() - a.template xy<R, -3, 3>() + a.template xy<R, -3, -3>() - a.template xy<R, 3, -3>()));
 }
 template <int R, class A> PC_DEV double dxz(const A &a, double fij)
 {
+  if (!a.bidiag()) return PC_DFULL(xz);
   return fij * (270.0 * (a.template xz<R, 1, 1>() - a.template xz<R, -1, 1>() + a.template xz<R, -1, -1>() - a.template xz<R, 1, -1>())
                 - 27.0 * (a.template xz<R, 2, 2>() - a.template xz<R, -2, 2>() + a.template xz<R, -2, -2>() - a.template xz<R, 2, -2>())
                 + 2.0 * (a.template xz<R, 3, 3>() - a.template xz<R, -3, 3>() + a.template xz<R, -3, -3>() - a.template xz<R, 3, -3>()));
 }
 template <int R, class A> PC_DEV double dyz(const A &a, double fij)
 {
+  if (!a.bidiag()) return PC_DFULL(yz);
   return fij * (270.0 * (a.template yz<R, 1, 1>() - a.template yz<R, -1, 1>() + a.template yz<R, -1, -1>() - a.template yz<R, 1, -1>())
                 - 27.0 * (a.template yz<R, 2, 2>() - a.template yz<R, -2, 2>() + a.template yz<R, -2, -2>() - a.template yz<R, 2, -2>())
                 + 2.0 * (a.template yz<R, 3, 3>() - a.template yz<R, -3, 3>() + a.template yz<R, -3, -3>() - a.template yz<R, 3, -3>()));
 }
+#undef PC_DFULL
+#undef PC_DROW
 
 // per-cell by-products for the CFL step and the 0-D diagnostics
 struct CellAux {

@@ -61,6 +61,9 @@ CASES = {
     "mhd_ragged": lambda pk: pk.setups.make_params(40, 20, 12, magnetic=True, nu=5e-3, eta=4e-3, cdt=0.4, cdtv=0.3),
     "hydro_upwind": lambda pk: pk.setups.config_hydro(32, lupw_lnrho=1, lupw_uu=1),
     "convslab": lambda pk: pk.setups.config_convslab(32, 32, 32),
+    # lbidiagonal_derij=F, as samples/gputest/run.in sets: 36-point product derij (deriv.f90:1430-1557)
+    "mhd_derij36": lambda pk: pk.setups.config_mhd(32, lbidiagonal_derij=0),
+    "mhd_entropy_derij36": lambda pk: pk.setups.config_mhd_entropy(32, lbidiagonal_derij=0),
 }
 
 
@@ -147,7 +150,10 @@ def test_fixed_dt(pk, orc, dev):
 
 def test_unsupported_is_refused(pk, dev):
     P, zprof, grid = pk.setups.config_mhd(32)
-    P.lbidiagonal_derij = 0
+    P.ldensity = 0                      # no GPU implementation without the density module
+    with pytest.raises(pk.PCB200Error):
+        dev.initialize_GPU(P, zprof)
+    P, zprof, grid = pk.setups.make_params(31, 32, 32, lbidiagonal_derij=0)   # odd mx: no TMA kernel for the 36-point derij
     with pytest.raises(pk.PCB200Error):
         dev.initialize_GPU(P, zprof)
 

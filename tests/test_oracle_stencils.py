@@ -66,3 +66,16 @@ def test_der_modified_wavenumber(orc):
     a = k * dx
     keff = (45 * np.sin(a) - 9 * np.sin(2 * a) + np.sin(3 * a)) / (30 * dx)
     assert np.allclose(got, keff * np.cos(k * x[NG:-NG]), atol=1e-13)
+
+
+@pytest.mark.parametrize("ij", [(1, 2), (2, 3), (3, 1)])
+def test_derij_36point_is_exact_for_degree6_products(orc, ij):
+    """lbidiagonal_derij=F (deriv.f90:1430-1557): product of two 6th-order first-derivative
+    stencils, exact for x^a y^b with a, b <= 6, and equal to der_j(der_i f) by construction."""
+    i, j = ij
+    f, (X, Y, Z), d = field_from(lambda x, y, z: x ** 6 * y ** 5 + y ** 6 * z ** 4 - 2 * z ** 6 * x ** 3 + x * y * z)
+    got = orc.derij_full(f, i, j, 1.0 / d[i - 1], 1.0 / d[j - 1])
+    exact = {(1, 2): 30 * X ** 5 * Y ** 4 + Z, (2, 3): 24 * Y ** 5 * Z ** 3 + X, (3, 1): -36 * Z ** 5 * X ** 2 + Y}[ij]
+    assert np.abs(got - exact).max() < 1e-10 * max(1.0, np.abs(exact).max())
+    bid = orc.derij(f, i, j, 1.0 / d[i - 1], 1.0 / d[j - 1])
+    assert np.abs(bid - exact).max() > 1e-8          # the bidiagonal scheme is a different discretisation
