@@ -7,14 +7,18 @@
 //   [stable radix sort of (key, index) by the pencil index imn, particles_map.f90:986-1163]
 //   part_gather       fp, dfp, ipar, ineargrid permuted into pencil order
 //   part_pencil_bounds  k1_imn, k2_imn             (particles_map.f90:1920-1948)
-//   part_map_xxp      np and TSC rhop               (particles_map.f90:1295-1742)
+//   part_cellkey      cell id of every particle + count per cell (= np, map_xxp_grid :1322-1327)
+//   [second stable sort by cell id -> cell bins; exclusive scan of the counts -> bin offsets]
 //   part_drag         dxxp_dt_pencil/dvvp_dt_pencil (particles_dust.f90:3918-4911): spline
-//                     interpolation of u, drag, TSC back-reaction, CFL; dxxp_dt, dvvp_dt (:3120,:3199)
+//                     interpolation of u, drag, CFL; dxxp_dt, dvvp_dt (:3120,:3199)
 //   part_dt_cells     dt1_drag per cell             (particles_dust.f90:4843-4910)
-//   part_backreact    adds the deposited drag to the 2N register / new state of u
+//   part_deposit      TSC back-reaction (:4443-4536) and TSC rhop (particles_map.f90:1560-1640)
+//                     as a GATHER: one thread per grid cell walks the particles of its 27
+//                     neighbour bins.  No atomics, fixed summation order => deterministic.
+//                     The result joins the 2N register / new state of u (equ.f90:1046).
 //   part_second       particles_timestep_second  (particles_main.f90:521)
 // Layout = the reference's: fp[6][mpar] (particle index fastest), ineargrid[3][mpar] 1-based.
-// Deposits wrap at scatter time in locally periodic directions, which is fold_df/fold_f
+// The gather reads a neighbour bin through the periodic wrap, which is fold_df/fold_f
 // (ghostfold_mpicomm.f90:46-124) without the intermediate ghost layer.
 #pragma once
 
@@ -108,51 +112,36 @@ __device__ __forceinline__ double part_tsc(const PartPar &q, int ax, double xp, 
   const double b = (xp - xg) * q.h_1[ax];
   return 0.75 - b * b;
 }
-// index of a deposit target: wrapped back into the interior where the direction folds locally
-__device__ __forceinline__ int part_fold(int i, int n, int wrap)
-{
-  if (!wrap) return i;
-  return i < NG ? i + n : (i >= NG + n ? i - n : i);
-}
-
-__global__ void part_map_xxp(PartPar q, const double *__restrict__ fp, const int *__restrict__ inear,
-                             int *__restrict__ np_i, double *__restrict__ rhop)
+// interior-relative cell id of the nearest grid point; ccount = particles per cell (exact)
+__global__ void part_cellkey(int npar, int mpar, const int *__restrict__ inear, unsigned *__restrict__ ckeys,
+                             unsigned *__restrict__ cvals, int *__restrict__ ccount)
 {
   const DevPar &c = c_par;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= q.npar) return;
-  const int i0[3] = {inear[k] - 1, inear[(size_t)q.mpar + k] - 1, inear[(size_t)2 * q.mpar + k] - 1};
-  const double xp[3] = {fp[k], fp[(size_t)q.mpar + k], fp[(size_t)2 * q.mpar + k]};
-  atomicAdd(&np_i[(long long)i0[2] * c.sz + (long long)i0[1] * c.sy + i0[0]], 1);
-  double wx[3], wy[3], wz[3];
-#pragma unroll
-  for (int d = 0; d < 3; d++) {
-    wx[d] = part_tsc(q, 0, xp[0], i0[0] + d - 1, i0[0]);
-    wy[d] = part_tsc(q, 1, xp[1], i0[1] + d - 1, i0[1]);
-    wz[d] = part_tsc(q, 2, xp[2], i0[2] + d - 1, i0[2]);
-  }
-#pragma unroll
-  for (int dz = 0; dz < 3; dz++) {
-    const long long oz = (long long)part_fold(i0[2] + dz - 1, c.nz, q.wrap[2]) * c.sz;
-#pragma unroll
-    for (int dy = 0; dy < 3; dy++) {
-      const long long oy = oz + (long long)part_fold(i0[1] + dy - 1, c.ny, q.wrap[1]) * c.sy;
-#pragma unroll
-      for (int dx = 0; dx < 3; dx++)
-        atomicAdd(&rhop[oy + part_fold(i0[0] + dx - 1, c.nx, q.wrap[0])], (wx[dx] * wy[dy]) * wz[dz]);
-    }
-  }
+  if (k >= npar) return;
+  const int l = inear[k] - 1 - NG, m = inear[(size_t)mpar + k] - 1 - NG, n = inear[(size_t)2 * mpar + k] - 1 - NG;
+  const unsigned id = (unsigned)((n * c.ny + m) * c.nx + l);
+  ckeys[k] = id; cvals[k] = (unsigned)k;
+  atomicAdd(&ccount[id], 1);
+}
+
+// rank[k] = position of particle k in the cell-sorted list
+__global__ void part_invperm(int npar, const unsigned *__restrict__ perm, unsigned *__restrict__ rank)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < npar) rank[perm[i]] = (unsigned)i;
 }
 
 __device__ __forceinline__ void atomic_max_nonneg(double *addr, double v)   // exact for v >= 0
 { atomicMax(reinterpret_cast<unsigned long long *>(addr), (unsigned long long)__double_as_longlong(v)); }
 
-// One thread per particle.  f = state of this substep with valid ghost zones; dfu[3][mw]
-// receives the back-reaction (zeroed before the launch); dt1 (one double) takes the
-// advective particle CFL term when ldt.
+// One thread per particle.  f = state of this substep with valid ghost zones; csort[6][mpar]
+// receives position and drag force in CELL-SORTED order (slot rank[k]) for part_deposit;
+// dt1 (one double) takes the advective particle CFL term when ldt.
 __global__ void __launch_bounds__(128) part_drag(PartPar q, const double *__restrict__ f, const double *__restrict__ fp,
                                                   double *__restrict__ dfp, const int *__restrict__ inear,
-                                                  double *__restrict__ dfu, double *__restrict__ dt1, int ldt)
+                                                  const unsigned *__restrict__ rank, double *__restrict__ csort,
+                                                  double *__restrict__ dt1, int ldt)
 {
   const DevPar &c = c_par;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -196,31 +185,16 @@ __global__ void __launch_bounds__(128) part_drag(PartPar q, const double *__rest
       double drag[3];
 #pragma unroll
       for (int j = 0; j < 3; j++) { drag[j] = -q.tausp1 * (vp[j] - uup[j]); dvp[j] = drag[j]; }   // :4264
-      if (q.ldrag_gas) {                                            // TSC back-reaction :4443-4536
-        double wx[3], wy[3], wz[3];
+      if (q.ldrag_gas) {                                            // consumed by part_deposit
+        const unsigned r = rank[k];
 #pragma unroll
-        for (int d = 0; d < 3; d++) {
-          wx[d] = part_tsc(q, 0, xp[0], i0[0] + d - 1, i0[0]);
-          wy[d] = part_tsc(q, 1, xp[1], i0[1] + d - 1, i0[1]);
-          wz[d] = part_tsc(q, 2, xp[2], i0[2] + d - 1, i0[2]);
-        }
-        const double *lnrho = f + (long long)q.ilnrho * c.mw;
-#pragma unroll
-        for (int dz = 0; dz < 3; dz++)
-#pragma unroll
-          for (int dy = 0; dy < 3; dy++)
-#pragma unroll
-            for (int dx = 0; dx < 3; dx++) {
-              // gas density at the (unfolded) target: ghost zones of f hold the periodic image
-              const long long src = c0 + (long long)(dz - 1) * c.sz + (long long)(dy - 1) * c.sy + dx - 1;
-              const long long dst = (long long)part_fold(i0[2] + dz - 1, c.nz, q.wrap[2]) * c.sz
-                                  + (long long)part_fold(i0[1] + dy - 1, c.ny, q.wrap[1]) * c.sy
-                                  + part_fold(i0[0] + dx - 1, c.nx, q.wrap[0]);
-              const double fac = -q.rhop_swarm * exp(-__ldg(lnrho + src)) * ((wx[dx] * wy[dy]) * wz[dz]);
-#pragma unroll
-              for (int j = 0; j < 3; j++) atomicAdd(dfu + (long long)j * c.mw + dst, fac * drag[j]);
-            }
+        for (int j = 0; j < 3; j++) csort[(size_t)(3 + j) * M + r] = drag[j];
       }
+    }
+    {
+      const unsigned r = rank[k];
+#pragma unroll
+      for (int j = 0; j < 3; j++) csort[(size_t)j * M + r] = xp[j];
     }
     if (q.lcoriolis && q.Omega2 != 0.0) { dvp[0] += q.Omega2 * vp[1]; dvp[1] -= q.Omega2 * vp[0]; }   // dvvp_dt :3226-3233
 #pragma unroll
@@ -237,15 +211,15 @@ __global__ void __launch_bounds__(128) part_drag(PartPar q, const double *__rest
 
 // dt1_drag = (max_k tausp1 + sum_k mp_vcell*rho1*tausp1)/cdtp_drag per cell with particles
 // (particles_dust.f90:4843-4847, 4901-4910); constant tausp => the sum is np * (...)
-__global__ void part_dt_cells(PartPar q, const double *__restrict__ f, const int *__restrict__ np_i, double *__restrict__ dt1)
+__global__ void part_dt_cells(PartPar q, const double *__restrict__ f, const int *__restrict__ ccount, double *__restrict__ dt1)
 {
   const DevPar &c = c_par;
   const int l = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y, n = blockIdx.z;
   double d = 0.0;
   if (l < c.nx) {
-    const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
-    const int npc = np_i[i];
+    const int npc = ccount[(n * c.ny + m) * c.nx + l];
     if (npc > 0) {
+      const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
       d = q.tausp1;
       if (q.ldrag_gas) d += npc * (q.rhop_swarm * exp(-f[(long long)q.ilnrho * c.mw + i]) * q.tausp1);
       d /= q.cdtp_drag;
@@ -255,21 +229,76 @@ __global__ void part_dt_cells(PartPar q, const double *__restrict__ f, const int
   if ((threadIdx.x & 31) == 0 && d > 0.0) atomic_max_nonneg(dt1, d);
 }
 
-// w_u += dfu ; f_out_u += beta*dt*dfu  (the deposit is part of df before the 2N update,
-// equ.f90:1046 + timestep.f90:162); f_out == nullptr when the update is done by axpy_update
-__global__ void part_backreact(int iux, const double *__restrict__ dfu, double *__restrict__ w, double *__restrict__ f_out,
-                               const double *__restrict__ dt_dev, double beta)
+// One thread per interior cell (l,m,n): gathers from the particles whose nearest grid point is
+// one of the 27 neighbours.  csort[6][mpar] = x,y,z,drag of the particles in cell-sorted order,
+// cs = exclusive scan of the per-cell counts, so the three x-neighbour bins of one (y,z) row
+// are ONE contiguous range (plus one wrapped bin at the x edges).  The TSC weight of this grid
+// point for a particle at distance a (in cells) is 0.75-a^2 if it is the particle's nearest
+// point (|a|<=1/2) and 1.125-1.5|a|+a^2/2 otherwise (particles_dust.f90:4467-4490; the two
+// forms agree at |a|=1/2).  In y,z (and the wrapped x bin) the distance is taken to the image
+// of this grid point next to the bin, i.e. through the periodic fold (ghostfold_mpicomm.f90:46-124).
+//   rhop[c]  = sum of weights                          (particles_map.f90:1631, times rhop_swarm on output)
+//   dfu_j    = -rhop_swarm/rho(c) * sum_k w_k drag_kj   (particles_dust.f90:4527)
+//   w_u += dfu ; f_out_u += beta*dt*dfu                (equ.f90:1046 + timestep.f90:162; f_out may be null)
+__device__ __forceinline__ double part_w(double a)
+{ const double b = fabs(a); return b <= 0.5 ? 0.75 - a * a : 1.125 - 1.5 * b + 0.5 * (a * a); }
+
+__global__ void __launch_bounds__(128) part_deposit(PartPar q, const double *__restrict__ f, const double *__restrict__ csort,
+                                                     const int *__restrict__ cs, double *__restrict__ rhop,
+                                                     double *__restrict__ w, double *__restrict__ f_out,
+                                                     const double *__restrict__ dt_dev, double beta)
 {
   const DevPar &c = c_par;
-  const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  const int m = blockIdx.y;
-  const int n = blockIdx.z % c.nz, j = blockIdx.z / c.nz;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y, n = blockIdx.z;
   if (l >= c.nx) return;
+  const size_t M = q.mpar;
+  const double xg = q.x0_loc[0] + l * q.h[0];
+  // x bins of the main range and of the wrapped bin (if this cell sits at an x edge)
+  const int la = l > 0 ? l - 1 : 0, lb = l < c.nx - 1 ? l + 1 : c.nx - 1;
+  const int lw = l == 0 ? c.nx - 1 : (l == c.nx - 1 ? 0 : -1);
+  const double xgw = l == 0 ? xg + q.Lxyz[0] : xg - q.Lxyz[0];      // image of this point seen from the wrapped bin
+  int r0[9], r1[9], w0[9], w1[9];
+#pragma unroll
+  for (int j = 0; j < 9; j++) {
+    const int oz = j / 3 - 1, oy = j % 3 - 1;
+    int nn = n + oz; nn = nn < 0 ? nn + c.nz : (nn >= c.nz ? nn - c.nz : nn);
+    int mm = m + oy; mm = mm < 0 ? mm + c.ny : (mm >= c.ny ? mm - c.ny : mm);
+    const int row = (nn * c.ny + mm) * c.nx;
+    r0[j] = __ldg(cs + row + la); r1[j] = __ldg(cs + row + lb + 1);
+    w0[j] = lw >= 0 ? __ldg(cs + row + lw) : 0; w1[j] = lw >= 0 ? __ldg(cs + row + lw + 1) : 0;
+  }
+  double v0 = 0.0, v1 = 0.0, v2 = 0.0, ws = 0.0;
+#pragma unroll
+  for (int j = 0; j < 9; j++) {
+    const int oz = j / 3 - 1, oy = j % 3 - 1;
+    int nn = n + oz; nn = nn < 0 ? nn + c.nz : (nn >= c.nz ? nn - c.nz : nn);
+    int mm = m + oy; mm = mm < 0 ? mm + c.ny : (mm >= c.ny ? mm - c.ny : mm);
+    const double zg = q.x0_loc[2] + (nn - oz) * q.h[2], yg = q.x0_loc[1] + (mm - oy) * q.h[1];
+#pragma unroll 1
+    for (int pass = 0; pass < 2; pass++) {
+      const int i0 = pass ? w0[j] : r0[j], i1 = pass ? w1[j] : r1[j];
+      const double xgi = pass ? xgw : xg;
+      for (int i = i0; i < i1; i++) {
+        const double wt = (part_w((__ldg(csort + i) - xgi) * q.h_1[0]) * part_w((__ldg(csort + M + i) - yg) * q.h_1[1]))
+                          * part_w((__ldg(csort + 2 * M + i) - zg) * q.h_1[2]);
+        ws += wt;
+        if (q.ldrag_gas) { v0 += wt * __ldg(csort + 3 * M + i); v1 += wt * __ldg(csort + 4 * M + i); v2 += wt * __ldg(csort + 5 * M + i); }
+      }
+    }
+  }
   const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
-  const double v = dfu[(long long)j * c.mw + i];
-  const long long o = (long long)(iux + j) * c.mw + i;
-  w[o] += v;
-  if (f_out) f_out[o] += (beta * dt_dev[0]) * v;
+  rhop[i] = ws;
+  if (q.ldrag_gas) {
+    const double fac = -q.rhop_swarm * exp(-f[(long long)q.ilnrho * c.mw + i]);
+    const double bdt = f_out ? beta * dt_dev[0] : 0.0;
+    const double d[3] = {fac * v0, fac * v1, fac * v2};
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const long long o = (long long)(q.iux + j) * c.mw + i;
+      w[o] += d[j];
+      if (f_out) f_out[o] += bdt * d[j];
+    }
+  }
 }
 
 __global__ void part_second(double *__restrict__ fp, const double *__restrict__ dfp, int npar, int mpar,
@@ -282,12 +311,16 @@ __global__ void part_second(double *__restrict__ fp, const double *__restrict__ 
   for (int j = 0; j < 6; j++) fp[(size_t)j * mpar + k] = fp[(size_t)j * mpar + k] + dtb * dfp[(size_t)j * mpar + k];
 }
 
-// aux fields for the host: np as doubles, rhop scaled by rhop_swarm (particles_map.f90:1733-1737)
-__global__ void part_aux_out(long long mw, const int *__restrict__ np_i, const double *__restrict__ rhop, double rhop_swarm,
+// aux fields for the host on the padded grid: np (count at the nearest point) and
+// rhop = rhop_swarm * sum of TSC weights (particles_map.f90:1733-1737)
+__global__ void part_aux_out(const int *__restrict__ ccount, const double *__restrict__ rhop, double rhop_swarm,
                              double *__restrict__ np_out, double *__restrict__ rhop_out)
 {
+  const DevPar &c = c_par;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= mw) return;
-  np_out[i] = (double)np_i[i];
-  rhop_out[i] = rhop_swarm * rhop[i];
+  if (i >= c.mw) return;
+  const int l = (int)(i % c.mx) - NG, m = (int)((i / c.mx) % c.my) - NG, n = (int)(i / c.sz) - NG;
+  const bool in = l >= 0 && l < c.nx && m >= 0 && m < c.ny && n >= 0 && n < c.nz;
+  np_out[i] = in ? (double)ccount[(n * c.ny + m) * c.nx + l] : 0.0;
+  rhop_out[i] = in ? rhop_swarm * rhop[i] : 0.0;
 }

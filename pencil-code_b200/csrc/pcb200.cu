@@ -8,6 +8,7 @@
 #include "kernels.cuh"
 #include "particles.cuh"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -76,8 +77,11 @@ struct Ctx {
     double *fp[2] = {nullptr, nullptr}, *dfp[2] = {nullptr, nullptr};
     int *ipar[2] = {nullptr, nullptr}, *inear[2] = {nullptr, nullptr};
     unsigned *keys[2] = {nullptr, nullptr}, *vals[2] = {nullptr, nullptr};
-    int *imn_array = nullptr, *k1 = nullptr, *k2 = nullptr, *np_i = nullptr;
-    double *rhop = nullptr, *dfu = nullptr, *dt1 = nullptr;
+    int *imn_array = nullptr, *k1 = nullptr, *k2 = nullptr;
+    int ncell = 0, cell_bits = 1;
+    unsigned *ckeys[2] = {nullptr, nullptr}, *cvals[2] = {nullptr, nullptr};   // second sort: by cell
+    int *ccount = nullptr, *cs = nullptr;                                      // per-cell count, exclusive scan (ncell+1)
+    double *rhop = nullptr, *drag = nullptr, *aux = nullptr, *dt1 = nullptr;
     void *cub_tmp = nullptr; size_t cub_bytes = 0;
   } part;
   double *face[4] = {nullptr, nullptr, nullptr, nullptr};   // send lo/hi, recv lo/hi for the packed x,y faces
@@ -510,14 +514,10 @@ static int launch_rhs(int auxm, const SubstepArgs &a, int z_lo, int z_hi, size_t
 static void part_free()
 {
   Ctx::Part &p = g.part;
-  for (int i = 0; i < 2; i++) {
-    if (p.fp[i]) cudaFree(p.fp[i]); if (p.dfp[i]) cudaFree(p.dfp[i]); if (p.ipar[i]) cudaFree(p.ipar[i]);
-    if (p.inear[i]) cudaFree(p.inear[i]); if (p.keys[i]) cudaFree(p.keys[i]); if (p.vals[i]) cudaFree(p.vals[i]);
-    p.fp[i] = p.dfp[i] = nullptr; p.ipar[i] = p.inear[i] = nullptr; p.keys[i] = p.vals[i] = nullptr;
-  }
-  if (p.imn_array) cudaFree(p.imn_array); if (p.k1) cudaFree(p.k1); if (p.k2) cudaFree(p.k2); if (p.np_i) cudaFree(p.np_i);
-  if (p.rhop) cudaFree(p.rhop); if (p.dfu) cudaFree(p.dfu); if (p.dt1) cudaFree(p.dt1); if (p.cub_tmp) cudaFree(p.cub_tmp);
-  p.imn_array = p.k1 = p.k2 = p.np_i = nullptr; p.rhop = p.dfu = p.dt1 = nullptr; p.cub_tmp = nullptr; p.cub_bytes = 0;
+  auto fr = [](auto *&q) { if (q) cudaFree(q); q = nullptr; };
+  for (int i = 0; i < 2; i++) { fr(p.fp[i]); fr(p.dfp[i]); fr(p.ipar[i]); fr(p.inear[i]); fr(p.keys[i]); fr(p.vals[i]); fr(p.ckeys[i]); fr(p.cvals[i]); }
+  fr(p.imn_array); fr(p.k1); fr(p.k2); fr(p.ccount); fr(p.cs); fr(p.rhop); fr(p.drag); fr(p.aux); fr(p.dt1); fr(p.cub_tmp);
+  p.cub_bytes = 0;
   p.on = false;
 }
 
@@ -583,14 +583,25 @@ extern "C" int pcb200_particles_initialize(const pcb200_particle_params *pp)
   CK(cudaMalloc(&p.imn_array, imn.size() * sizeof(int)));
   CK(cudaMemcpyAsync(p.imn_array, imn.data(), imn.size() * sizeof(int), cudaMemcpyHostToDevice, g.st));
   CK(cudaMalloc(&p.k1, p.nimn * sizeof(int))); CK(cudaMalloc(&p.k2, p.nimn * sizeof(int)));
-  CK(cudaMalloc(&p.np_i, (size_t)h.mw * sizeof(int))); CK(cudaMalloc(&p.rhop, (size_t)h.mw * sizeof(double)));
-  CK(cudaMalloc(&p.dfu, (size_t)3 * h.mw * sizeof(double))); CK(cudaMalloc(&p.dt1, sizeof(double)));
-  CK(cudaMemsetAsync(p.np_i, 0, (size_t)h.mw * sizeof(int), g.st));
+  p.ncell = P.nx * P.ny * P.nz;
+  p.cell_bits = 1; while ((1LL << p.cell_bits) < p.ncell) p.cell_bits++;
+  for (int i = 0; i < 2; i++) { CK(cudaMalloc(&p.ckeys[i], M * sizeof(unsigned))); CK(cudaMalloc(&p.cvals[i], M * sizeof(unsigned))); }
+  CK(cudaMalloc(&p.ccount, (size_t)p.ncell * sizeof(int))); CK(cudaMalloc(&p.cs, ((size_t)p.ncell + 1) * sizeof(int)));
+  CK(cudaMalloc(&p.rhop, (size_t)h.mw * sizeof(double))); CK(cudaMalloc(&p.drag, 6 * M * sizeof(double)));   // csort[6][mpar]
+  CK(cudaMalloc(&p.aux, (size_t)2 * h.mw * sizeof(double))); CK(cudaMalloc(&p.dt1, sizeof(double)));
+  CK(cudaMemsetAsync(p.ccount, 0, (size_t)p.ncell * sizeof(int), g.st));
+  CK(cudaMemsetAsync(p.cs, 0, ((size_t)p.ncell + 1) * sizeof(int), g.st));
   CK(cudaMemsetAsync(p.rhop, 0, (size_t)h.mw * sizeof(double), g.st));
   CK(cudaMemsetAsync(p.k1, 0, p.nimn * sizeof(int), g.st)); CK(cudaMemsetAsync(p.k2, 0, p.nimn * sizeof(int), g.st));
-  p.cub_bytes = 0;
-  CK(cub::DeviceRadixSort::SortPairs(nullptr, p.cub_bytes, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.npar, 0, p.key_bits, g.st));
+  {
+    size_t b1 = 0, b2 = 0, b3 = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, b1, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.npar, 0, p.key_bits, g.st));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, b2, p.ckeys[0], p.ckeys[1], p.cvals[0], p.cvals[1], q.npar, 0, p.cell_bits, g.st));
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, b3, p.ccount, p.cs, p.ncell, g.st));
+    p.cub_bytes = std::max(b1, std::max(b2, b3));
+  }
   CK(cudaMalloc(&p.cub_tmp, p.cub_bytes ? p.cub_bytes : 16));
+  CK(cudaMemcpyAsync(p.cs + p.ncell, &q.npar, sizeof(int), cudaMemcpyHostToDevice, g.st));   // after the memset above, same stream
   CK(cudaStreamSynchronize(g.st));
   p.cur = 0; p.on = true;
   return PCB200_OK;
@@ -630,8 +641,8 @@ extern "C" int pcb200_particles_get_aux(double *np, double *rhop)
   if (!p.on) return fail(PCB200_ESTATE, "pcb200_particles_get_aux: particles are not initialised");
   if (!np || !rhop) return fail(PCB200_EARG, "null aux arrays");
   const long long mw = g.hp.mw;
-  double *tmp = p.dfu;      // scratch between substeps: dfu is rebuilt by every substep
-  part_aux_out<<<(unsigned)((mw + 255) / 256), 256, 0, g.st>>>(mw, p.np_i, p.rhop, p.q.rhop_swarm, tmp, tmp + mw);
+  double *tmp = p.aux;
+  part_aux_out<<<(unsigned)((mw + 255) / 256), 256, 0, g.st>>>(p.ccount, p.rhop, p.q.rhop_swarm, tmp, tmp + mw);
   g.launches++;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(np, tmp, mw * sizeof(double), cudaMemcpyDeviceToHost, g.st));
@@ -657,25 +668,32 @@ static int part_before_rhs(int isub)
   p.cur = nx;
   CK(cudaMemsetAsync(p.k1, 0, p.nimn * sizeof(int), g.st)); CK(cudaMemsetAsync(p.k2, 0, p.nimn * sizeof(int), g.st));
   part_pencil_bounds<<<nb, 256, 0, g.st>>>(q.npar, p.keys[1], p.k1, p.k2);
-  CK(cudaMemsetAsync(p.np_i, 0, (size_t)h.mw * sizeof(int), g.st));
-  CK(cudaMemsetAsync(p.rhop, 0, (size_t)h.mw * sizeof(double), g.st));
-  part_map_xxp<<<nb, 256, 0, g.st>>>(q, p.fp[p.cur], p.inear[p.cur], p.np_i, p.rhop);
-  g.launches += 3;
+  // cell bins for the gather-deposit: count per cell (= np), particles sorted by cell, bin offsets
+  CK(cudaMemsetAsync(p.ccount, 0, ((size_t)p.ncell) * sizeof(int), g.st));
+  part_cellkey<<<nb, 256, 0, g.st>>>(q.npar, q.mpar, p.inear[p.cur], p.ckeys[0], p.cvals[0], p.ccount);
+  g.launches += 2;
   CK(cudaGetLastError());
+  bytes = p.cub_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(p.cub_tmp, bytes, p.ckeys[0], p.ckeys[1], p.cvals[0], p.cvals[1], q.npar, 0, p.cell_bits, g.st));
+  part_invperm<<<nb, 256, 0, g.st>>>(q.npar, p.cvals[1], p.cvals[0]);      // cvals[0] := rank of each particle in its bin list
+  g.launches++;
+  bytes = p.cub_bytes;
+  // cs[ncell] = npar was set once at initialisation
+  CK(cub::DeviceScan::ExclusiveSum(p.cub_tmp, bytes, p.ccount, p.cs, p.ncell, g.st));
+  (void)h;
   return PCB200_OK;
 }
 
 // the particle share of the mn-loop (equ.f90:1046) + dxxp_dt/dvvp_dt (:379-382): needs valid ghost zones
 static int part_pencils(const double *fin, int ldt)
 {
-  Ctx::Part &p = g.part; const PartPar &q = p.q; const DevPar &h = g.hp; const pcb200_params &P = g.P;
-  CK(cudaMemsetAsync(p.dfu, 0, (size_t)3 * h.mw * sizeof(double), g.st));
+  Ctx::Part &p = g.part; const PartPar &q = p.q; const pcb200_params &P = g.P;
   if (ldt) CK(cudaMemsetAsync(p.dt1, 0, sizeof(double), g.st));
-  part_drag<<<(unsigned)((q.npar + 127) / 128), 128, 0, g.st>>>(q, fin, p.fp[p.cur], p.dfp[p.cur], p.inear[p.cur], p.dfu, p.dt1, ldt);
+  part_drag<<<(unsigned)((q.npar + 127) / 128), 128, 0, g.st>>>(q, fin, p.fp[p.cur], p.dfp[p.cur], p.inear[p.cur], p.cvals[0], p.drag, p.dt1, ldt);
   g.launches++;
   if (ldt && q.ldrag_dust) {
     dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
-    part_dt_cells<<<grd, blk, 0, g.st>>>(q, fin, p.np_i, p.dt1);
+    part_dt_cells<<<grd, blk, 0, g.st>>>(q, fin, p.ccount, p.dt1);
     g.launches++;
   }
   CK(cudaGetLastError());
@@ -749,11 +767,12 @@ static int do_substep(int isub, int ldiagnos)
     if ((rc = launch_rhs(auxm, a, 0, NG, nb0, &nb1))) return rc;
     if ((rc = launch_rhs(auxm, a, P.nz - NG, P.nz, (size_t)nb0 + nb1, &nb2))) return rc;
   }
-  if (g.part.on && g.part.q.ldrag_gas) {
-    // the deposited drag is part of df (equ.f90:1046): add it to the 2N register and, when this
-    // launch already produced the new state, to f_out as well (otherwise axpy_update does)
-    dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz * 3);
-    part_backreact<<<grd, blk, 0, g.st>>>(P.iux - 1, g.part.dfu, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
+  if (g.part.on) {
+    // TSC gather: rhop, and the drag back-reaction joins the 2N register and (when this launch
+    // already produced the new state) f_out; otherwise axpy_update carries it (equ.f90:1046)
+    Ctx::Part &pt = g.part;
+    dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
+    part_deposit<<<grd, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
     g.launches++;
     CK(cudaGetLastError());
   }
