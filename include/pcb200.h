@@ -256,6 +256,8 @@ int pcb200_particles_load(const double *fp, const int32_t *ipar);
  * (1-based first/last particle of each pencil in imn order, 0 if empty, particles_map.f90:1920) */
 int pcb200_particles_store(double *fp, double *dfp, int32_t *ipar, int32_t *ineargrid,
                            int32_t *k1_imn, int32_t *k2_imn);
+/* npar_loc now (it changes when particles migrate between ranks, particles_mpicomm.f90:267) */
+int pcb200_particles_count(int32_t *npar_loc);
 /* aux fields of map_xxp_grid on the full (mx,my,mz) grid: np and rhop */
 int pcb200_particles_get_aux(double *np, double *rhop);
 

@@ -491,19 +491,34 @@ __global__ void bc_fill(BcArgs b)
 // extent of the other two, so that the sequential x -> y -> z exchange carries edges and
 // corners without separate corner messages.  buf layout [var][c][b][NG planes] (axis 0) or
 // [var][iz][NG][mx] (axis 1).  unpack=1 scatters buf back into f.
-struct FaceArgs { double *f; double *buf; int axis, start, unpack; };
+struct FaceArgs { double *f; double *buf; int axis, start, unpack, nplanes; };   // unpack: 0 pack, 1 copy back, 2 add back
 __global__ void face_copy(FaceArgs a)
 {
   const DevPar &c = c_par;
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long per_var = a.axis == 0 ? (long long)NG * c.my * c.mz : (long long)NG * c.mx * c.mz;
+  const int np = a.nplanes;
+  const long long per_var = a.axis == 0 ? (long long)np * c.my * c.mz : (a.axis == 1 ? (long long)np * c.mx * c.mz : (long long)np * c.mx * c.my);
   if (t >= per_var) return;
   int ix, iy, iz;
-  if (a.axis == 0) { ix = a.start + (int)(t % NG); const long long r = t / NG; iy = (int)(r % c.my); iz = (int)(r / c.my); }
-  else { ix = (int)(t % c.mx); const long long r = t / c.mx; iy = a.start + (int)(r % NG); iz = (int)(r / NG); }
+  if (a.axis == 0) { ix = a.start + (int)(t % np); const long long r = t / np; iy = (int)(r % c.my); iz = (int)(r / c.my); }
+  else if (a.axis == 1) { ix = (int)(t % c.mx); const long long r = t / c.mx; iy = a.start + (int)(r % np); iz = (int)(r / np); }
+  else { ix = (int)(t % c.mx); const long long r = t / c.mx; iy = (int)(r % c.my); iz = a.start + (int)(r / c.my); }
   double *p = a.f + (long long)blockIdx.y * c.mw + (long long)iz * c.sz + (long long)iy * c.sy + ix;
   double *q = a.buf + (long long)blockIdx.y * per_var + t;
-  if (a.unpack) *p = *q; else *q = *p;
+  if (a.unpack == 0) *q = *p; else if (a.unpack == 1) *p = *q; else *p += *q;
+}
+// zero one plane (all blockIdx.y fields) -- the folded ghost layer (ghostfold_mpicomm.f90:69-70)
+__global__ void plane_zero(double *f, int axis, int plane)
+{
+  const DevPar &c = c_par;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long per = axis == 0 ? (long long)c.my * c.mz : (axis == 1 ? (long long)c.mx * c.mz : (long long)c.mx * c.my);
+  if (t >= per) return;
+  int ix, iy, iz;
+  if (axis == 0) { ix = plane; iy = (int)(t % c.my); iz = (int)(t / c.my); }
+  else if (axis == 1) { ix = (int)(t % c.mx); iy = plane; iz = (int)(t / c.mx); }
+  else { ix = (int)(t % c.mx); iy = (int)(t / c.mx); iz = plane; }
+  f[(long long)blockIdx.y * c.mw + (long long)iz * c.sz + (long long)iy * c.sy + ix] = 0.0;
 }
 
 // All locally periodic directions in one launch (bc_per_x/y/z, boundcond.f90:1813-1961).

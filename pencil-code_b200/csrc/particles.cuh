@@ -301,6 +301,71 @@ __global__ void __launch_bounds__(128) part_deposit(PartPar q, const double *__r
   }
 }
 
+// Multi-rank form of the gather.  Along a direction that is split between ranks the bins of
+// the neighbour rank are not here, so (as the reference does) the particles also deposit into
+// the FIRST GHOST LAYER and fold_df/fold_f ships that layer to the neighbour
+// (ghostfold_mpicomm.f90:46-153).  One thread per cell of the interior plus that layer;
+// acc[0] = sum of weights, acc[1..3] = sum of weight*drag, on the padded grid.
+__global__ void __launch_bounds__(128) part_deposit_ghost(PartPar q, const double *__restrict__ csort, const int *__restrict__ cs,
+                                                           double *__restrict__ acc)
+{
+  const DevPar &c = c_par;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x - 1, m = (int)blockIdx.y - 1, n = (int)blockIdx.z - 1;
+  if (l > c.nx) return;
+  if ((q.wrap[0] && (l < 0 || l >= c.nx)) || (q.wrap[1] && (m < 0 || m >= c.ny)) || (q.wrap[2] && (n < 0 || n >= c.nz))) return;
+  const size_t M = q.mpar;
+  double v0 = 0.0, v1 = 0.0, v2 = 0.0, ws = 0.0;
+#pragma unroll 1
+  for (int oz = -1; oz <= 1; oz++) {
+    int nn = n + oz;
+    if (nn < 0 || nn >= c.nz) { if (!q.wrap[2]) continue; nn = nn < 0 ? nn + c.nz : nn - c.nz; }
+    const double zg = q.x0_loc[2] + (nn - oz) * q.h[2];
+#pragma unroll 1
+    for (int oy = -1; oy <= 1; oy++) {
+      int mm = m + oy;
+      if (mm < 0 || mm >= c.ny) { if (!q.wrap[1]) continue; mm = mm < 0 ? mm + c.ny : mm - c.ny; }
+      const double yg = q.x0_loc[1] + (mm - oy) * q.h[1];
+#pragma unroll 1
+      for (int ox = -1; ox <= 1; ox++) {
+        int ll = l + ox;
+        if (ll < 0 || ll >= c.nx) { if (!q.wrap[0]) continue; ll = ll < 0 ? ll + c.nx : ll - c.nx; }
+        const double xg = q.x0_loc[0] + (ll - ox) * q.h[0];
+        const int id = (nn * c.ny + mm) * c.nx + ll;
+        const int i0 = __ldg(cs + id), i1 = __ldg(cs + id + 1);
+        for (int i = i0; i < i1; i++) {
+          const double wt = (part_w((__ldg(csort + i) - xg) * q.h_1[0]) * part_w((__ldg(csort + M + i) - yg) * q.h_1[1]))
+                            * part_w((__ldg(csort + 2 * M + i) - zg) * q.h_1[2]);
+          ws += wt;
+          if (q.ldrag_gas) { v0 += wt * __ldg(csort + 3 * M + i); v1 += wt * __ldg(csort + 4 * M + i); v2 += wt * __ldg(csort + 5 * M + i); }
+        }
+      }
+    }
+  }
+  const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+  acc[i] = ws; acc[c.mw + i] = v0; acc[2 * c.mw + i] = v1; acc[3 * c.mw + i] = v2;
+}
+
+// after the fold: rhop and the back-reaction from the accumulated sums (interior cells)
+__global__ void part_backreact_acc(PartPar q, const double *__restrict__ f, const double *__restrict__ acc, double *__restrict__ rhop,
+                                   double *__restrict__ w, double *__restrict__ f_out, const double *__restrict__ dt_dev, double beta)
+{
+  const DevPar &c = c_par;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y, n = blockIdx.z;
+  if (l >= c.nx) return;
+  const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+  rhop[i] = acc[i];
+  if (!q.ldrag_gas) return;
+  const double fac = -q.rhop_swarm * exp(-f[(long long)q.ilnrho * c.mw + i]);
+  const double bdt = f_out ? beta * dt_dev[0] : 0.0;
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const double d = fac * acc[(long long)(1 + j) * c.mw + i];
+    const long long o = (long long)(q.iux + j) * c.mw + i;
+    w[o] += d;
+    if (f_out) f_out[o] += bdt * d;
+  }
+}
+
 __global__ void part_second(double *__restrict__ fp, const double *__restrict__ dfp, int npar, int mpar,
                             const double *__restrict__ dt_dev, double beta)
 {
@@ -323,4 +388,142 @@ __global__ void part_aux_out(const int *__restrict__ ccount, const double *__res
   const bool in = l >= 0 && l < c.nx && m >= 0 && m < c.ny && n >= 0 && n < c.nz;
   np_out[i] = in ? (double)ccount[(n * c.ny + m) * c.nx + l] : 0.0;
   rhop_out[i] = in ? rhop_swarm * rhop[i] : 0.0;
+}
+
+// ------------------------------------------------------------------------
+// migrate_particles (particles_mpicomm.f90:267-696), device version.
+// Same bookkeeping order as the reference so that the per-rank storage order evolves the same
+// way: particles are scanned from the LAST to the first; a leaver's slot is refilled with the
+// current last particle (fp(k,:)=fp(npar_loc,:)); leavers are grouped by receiving rank in scan
+// order; arrivals are appended sender by sender in ascending rank order.
+// The sequential refill is equivalent to: with N' = N - nleave, the i-th largest hole below N'
+// receives the i-th largest survivor at or above N'.
+struct MigPar {
+  int np[3], ip[3], nloc[3];
+  int nslots, cap;            // distinct neighbour ranks; capacity of one message (particles)
+  int iproc;
+};
+enum { MIG_STAY = 31, MIG_NVAL = 13 };   // payload: fp(6), dfp(6), ipar
+
+// counters[0..26] leavers per slot, [27] nleave, [28] N', [29] error flags, [30] new npar, [32..58] slot offsets
+__global__ void part_mig_classify(PartPar q, MigPar g, const double *__restrict__ fp, const int *__restrict__ slot_of_rank,
+                                  unsigned *__restrict__ rkeys, unsigned *__restrict__ rvals, int *__restrict__ leave,
+                                  int *__restrict__ counters)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= q.npar) return;
+  int rec[3];
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    const double x = fp[(size_t)a * q.mpar + k], xx = x - q.xyz0[a];
+    const double w = q.Lxyz[a] / g.np[a];                    // procx_bounds(j) = xyz0 + j*Lx/nprocx (grid.f90:835, linear grid)
+    const double x0l = g.ip[a] * w, x1l = (g.ip[a] + 1) * w; // xx0_loc, xx1_loc (:285-286)
+    int r = g.ip[a];
+    if (xx >= x1l && g.ip[a] < g.np[a] - 1) {
+      for (int j = g.ip[a] + 1; j <= g.np[a] - 1; j++) if (x < q.xyz0[a] + (j + 1) * w) { r = j; break; }
+    } else if (xx < x0l && g.ip[a] > 0) {
+      for (int j = g.ip[a] - 1; j >= 0; j--) if (x >= q.xyz0[a] + j * w) { r = j; break; }
+    }
+    rec[a] = r;
+  }
+  const int iproc_rec = rec[0] + g.np[0] * (rec[1] + g.np[1] * rec[2]);
+  unsigned key = MIG_STAY;
+  int lv = 0;
+  if (iproc_rec != g.iproc) {
+    const int s = slot_of_rank[iproc_rec];
+    if (s < 0) atomicOr(&counters[29], 1);                   // "wants to migrate to a processor that is not a neighbour" (:399)
+    else { key = (unsigned)s; lv = 1; atomicAdd(&counters[s], 1); }
+  }
+  leave[k] = lv;
+  const int r = q.npar - 1 - k;                              // scan order of the reference: k = npar_loc ... 1
+  rkeys[r] = key; rvals[r] = (unsigned)k;
+}
+
+__global__ void part_mig_offsets(MigPar g, int npar, int *__restrict__ counters)
+{
+  if (threadIdx.x || blockIdx.x) return;
+  int tot = 0;
+  for (int s = 0; s < g.nslots; s++) { counters[32 + s] = tot; tot += counters[s]; if (counters[s] > g.cap) atomicOr(&counters[29], 2); }
+  counters[27] = tot; counters[28] = npar - tot;
+}
+
+// sendbuf: [nslots][MIG_NVAL*cap + 1], last entry = count
+__global__ void part_mig_pack(MigPar g, int npar, int mpar, const unsigned *__restrict__ skeys, const unsigned *__restrict__ svals,
+                              const double *__restrict__ fp, const double *__restrict__ dfp, const int *__restrict__ ipar,
+                              const int *__restrict__ counters, double *__restrict__ sendbuf)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)MIG_NVAL * g.cap + 1;
+  if (i < g.nslots) sendbuf[(size_t)i * stride + (size_t)MIG_NVAL * g.cap] = (double)counters[i];
+  if (i >= counters[27] || i >= npar) return;
+  const unsigned s = skeys[i], k = svals[i];
+  const int j = i - counters[32 + s];
+  if (j >= g.cap) return;
+  double *b = sendbuf + (size_t)s * stride;
+#pragma unroll
+  for (int v = 0; v < 6; v++) { b[(size_t)v * g.cap + j] = fp[(size_t)v * mpar + k]; b[(size_t)(6 + v) * g.cap + j] = dfp[(size_t)v * mpar + k]; }
+  b[(size_t)12 * g.cap + j] = (double)ipar[k];
+}
+
+// pre = exclusive scan of leave.  holes[i] / tails[i]: see the header comment.
+__global__ void part_mig_holes(int npar, const int *__restrict__ leave, const int *__restrict__ pre, const int *__restrict__ counters,
+                               int *__restrict__ holes, int *__restrict__ tails)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= npar) return;
+  const int nleave = counters[27], nstay = counters[28];
+  if (leave[k]) {
+    if (k < nstay) { const int pre_n = nstay < npar ? pre[nstay] : nleave; holes[pre_n - pre[k] - 1] = k; }
+  } else if (k >= nstay) {
+    tails[(npar - 1 - k) - (nleave - pre[k])] = k;
+  }
+}
+__global__ void part_mig_fill(int npar, int mpar, const int *__restrict__ pre, const int *__restrict__ counters,
+                              const int *__restrict__ holes, const int *__restrict__ tails,
+                              double *__restrict__ fp, double *__restrict__ dfp, int *__restrict__ ipar)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nstay = counters[28], nleave = counters[27];
+  const int nholes = nstay < npar ? pre[nstay] : nleave;
+  if (i >= nholes) return;
+  const int d = holes[i], s = tails[i];
+#pragma unroll
+  for (int v = 0; v < 6; v++) { fp[(size_t)v * mpar + d] = fp[(size_t)v * mpar + s]; dfp[(size_t)v * mpar + d] = dfp[(size_t)v * mpar + s]; }
+  ipar[d] = ipar[s];
+}
+
+// arrivals: sender slots are in ascending rank order (":do i=0,ncpus-1" receive loop, :613)
+__global__ void part_mig_append(MigPar g, int mpar, const double *__restrict__ recvbuf, int *__restrict__ counters,
+                                double *__restrict__ fp, double *__restrict__ dfp, int *__restrict__ ipar)
+{
+  const int s = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)MIG_NVAL * g.cap + 1;
+  int off = counters[28], tot = counters[28];
+  for (int t = 0; t < g.nslots; t++) {
+    const int c = (int)recvbuf[(size_t)t * stride + (size_t)MIG_NVAL * g.cap];
+    if (t < s) off += c;
+    tot += c;
+  }
+  if (s == 0 && j == 0) { counters[30] = tot; if (tot > mpar) atomicOr(&counters[29], 4); }
+  const int cnt = (int)recvbuf[(size_t)s * stride + (size_t)MIG_NVAL * g.cap];
+  if (j >= cnt || off + j >= mpar) return;
+  const double *b = recvbuf + (size_t)s * stride;
+  const int d = off + j;
+#pragma unroll
+  for (int v = 0; v < 6; v++) { fp[(size_t)v * mpar + d] = b[(size_t)v * g.cap + j]; dfp[(size_t)v * mpar + d] = b[(size_t)(6 + v) * g.cap + j]; }
+  ipar[d] = (int)b[(size_t)12 * g.cap + j];
+}
+
+// periodic wrap only (boundconds_particles runs before migrate_particles, particles_sub.f90:135)
+__global__ void part_wrap(PartPar q, double *__restrict__ fp)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= q.npar) return;
+#pragma unroll
+  for (int ax = 0; ax < 3; ax++) {
+    double x = fp[(size_t)ax * q.mpar + k];
+    if (x < q.xyz0[ax]) x = x + q.Lxyz[ax];
+    if (x >= q.xyz0[ax] + q.Lxyz[ax]) x = x - q.Lxyz[ax];
+    fp[(size_t)ax * q.mpar + k] = x;
+  }
 }

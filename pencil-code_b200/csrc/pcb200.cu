@@ -82,6 +82,11 @@ struct Ctx {
     unsigned *ckeys[2] = {nullptr, nullptr}, *cvals[2] = {nullptr, nullptr};   // second sort: by cell
     int *ccount = nullptr, *cs = nullptr;                                      // per-cell count, exclusive scan (ncell+1)
     double *rhop = nullptr, *drag = nullptr, *aux = nullptr, *dt1 = nullptr;
+    // migration between ranks (migrate_particles)
+    MigPar mg; int nbr[27]; int *slot_of_rank = nullptr, *counters = nullptr, *leave = nullptr, *pre = nullptr, *holes = nullptr, *tails = nullptr;
+    double *sendbuf = nullptr, *recvbuf = nullptr; int *counters_host = nullptr;
+    double *acc = nullptr;                       // multi-rank deposit: [4][mw] sums incl. the first ghost layer
+    double *fold[4] = {nullptr, nullptr, nullptr, nullptr}; size_t fold_elems = 0;
     void *cub_tmp = nullptr; size_t cub_bytes = 0;
   } part;
   double *face[4] = {nullptr, nullptr, nullptr, nullptr};   // send lo/hi, recv lo/hi for the packed x,y faces
@@ -436,7 +441,7 @@ static int exchange_packed(double *f, int axis)
   const size_t cnt = (size_t)per_var * P.mvar;
   dim3 blk(256), grd((unsigned)((per_var + 255) / 256), P.mvar);
   auto copy = [&](double *buf, int start, int unpack) {
-    FaceArgs a; a.f = f; a.buf = buf; a.axis = axis; a.start = start; a.unpack = unpack;
+    FaceArgs a; a.f = f; a.buf = buf; a.axis = axis; a.start = start; a.unpack = unpack; a.nplanes = NG;
     face_copy<<<grd, blk, 0, g.st>>>(a);
     g.launches++;
   };
@@ -517,6 +522,10 @@ static void part_free()
   auto fr = [](auto *&q) { if (q) cudaFree(q); q = nullptr; };
   for (int i = 0; i < 2; i++) { fr(p.fp[i]); fr(p.dfp[i]); fr(p.ipar[i]); fr(p.inear[i]); fr(p.keys[i]); fr(p.vals[i]); fr(p.ckeys[i]); fr(p.cvals[i]); }
   fr(p.imn_array); fr(p.k1); fr(p.k2); fr(p.ccount); fr(p.cs); fr(p.rhop); fr(p.drag); fr(p.aux); fr(p.dt1); fr(p.cub_tmp);
+  fr(p.acc); for (int i = 0; i < 4; i++) fr(p.fold[i]);
+  fr(p.slot_of_rank); fr(p.counters); fr(p.leave); fr(p.pre); fr(p.holes); fr(p.tails); fr(p.sendbuf); fr(p.recvbuf);
+  if (p.counters_host) { cudaFreeHost(p.counters_host); p.counters_host = nullptr; }
+  p.fold_elems = 0;
   p.cub_bytes = 0;
   p.on = false;
 }
@@ -547,7 +556,6 @@ extern "C" int pcb200_particles_initialize(const pcb200_particle_params *pp)
   part_free();
   if (pp->npar_loc <= 0) return PCB200_OK;
   if (pp->mpar_loc < pp->npar_loc) return fail(PCB200_EARG, "mpar_loc < npar_loc");
-  if (g.nranks > 1) return fail(PCB200_EUNSUPP, "particles: migration/fold between ranks is not implemented (single rank only)");
   if (pp->ldragforce_dust_par && pp->tausp <= 0.0) return fail(PCB200_EARG, "particles: tausp must be > 0");
   const pcb200_params &P = g.P; const DevPar &h = g.hp;
   Ctx::Part &p = g.part;
@@ -595,12 +603,46 @@ extern "C" int pcb200_particles_initialize(const pcb200_particle_params *pp)
   CK(cudaMemsetAsync(p.k1, 0, p.nimn * sizeof(int), g.st)); CK(cudaMemsetAsync(p.k2, 0, p.nimn * sizeof(int), g.st));
   {
     size_t b1 = 0, b2 = 0, b3 = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, b1, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.npar, 0, p.key_bits, g.st));
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, b2, p.ckeys[0], p.ckeys[1], p.cvals[0], p.cvals[1], q.npar, 0, p.cell_bits, g.st));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, b1, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.mpar, 0, p.key_bits, g.st));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, b2, p.ckeys[0], p.ckeys[1], p.cvals[0], p.cvals[1], q.mpar, 0, p.cell_bits, g.st));
     CK(cub::DeviceScan::ExclusiveSum(nullptr, b3, p.ccount, p.cs, p.ncell, g.st));
     p.cub_bytes = std::max(b1, std::max(b2, b3));
   }
   CK(cudaMalloc(&p.cub_tmp, p.cub_bytes ? p.cub_bytes : 16));
+  if (g.nranks > 1) {
+    CK(cudaMalloc(&p.acc, (size_t)4 * h.mw * sizeof(double)));
+    const size_t pl = std::max((size_t)h.my * h.mz, std::max((size_t)h.mx * h.mz, (size_t)h.mx * h.my)) * 4;
+    for (int i = 0; i < 4; i++) CK(cudaMalloc(&p.fold[i], pl * sizeof(double)));
+    p.fold_elems = pl;
+    // neighbour ranks (26 offsets, periodic, distinct, ascending: the receive order of migrate_particles)
+    MigPar &mg = p.mg; memset(&mg, 0, sizeof(mg));
+    const int ipq[3] = {P.ipx, P.ipy, P.ipz};
+    for (int a = 0; a < 3; a++) { mg.np[a] = np[a]; mg.ip[a] = ipq[a]; mg.nloc[a] = nloc[a]; }
+    mg.iproc = g.rank;
+    std::vector<int> nb;
+    for (int dz = -1; dz <= 1; dz++) for (int dy = -1; dy <= 1; dy++) for (int dx = -1; dx <= 1; dx++) {
+      const int qx = (ipq[0] + dx + np[0]) % np[0], qy = (ipq[1] + dy + np[1]) % np[1], qz = (ipq[2] + dz + np[2]) % np[2];
+      const int r = qx + np[0] * (qy + np[1] * qz);
+      if (r != g.rank && std::find(nb.begin(), nb.end(), r) == nb.end()) nb.push_back(r);
+    }
+    std::sort(nb.begin(), nb.end());
+    mg.nslots = (int)nb.size();
+    const char *ce = getenv("PCB200_NPAR_MIG");
+    mg.cap = ce && atoi(ce) > 0 ? atoi(ce) : std::max(4096, pp->mpar_loc / 16);      // npar_mig of cparam.local
+    std::vector<int> sor(g.nranks, -1);
+    for (int i = 0; i < mg.nslots; i++) { p.nbr[i] = nb[i]; sor[nb[i]] = i; }
+    CK(cudaMalloc(&p.slot_of_rank, g.nranks * sizeof(int)));
+    CK(cudaMemcpy(p.slot_of_rank, sor.data(), g.nranks * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&p.counters, 64 * sizeof(int))); CK(cudaMallocHost(&p.counters_host, 64 * sizeof(int)));
+    CK(cudaMalloc(&p.leave, M * sizeof(int))); CK(cudaMalloc(&p.pre, (M + 1) * sizeof(int)));
+    CK(cudaMalloc(&p.holes, M * sizeof(int))); CK(cudaMalloc(&p.tails, M * sizeof(int)));
+    const size_t msg = (size_t)MIG_NVAL * mg.cap + 1;
+    CK(cudaMalloc(&p.sendbuf, msg * mg.nslots * sizeof(double))); CK(cudaMalloc(&p.recvbuf, msg * mg.nslots * sizeof(double)));
+    size_t b4 = 0, b5 = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, b4, p.leave, p.pre, pp->mpar_loc, g.st));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, b5, p.keys[0], p.keys[1], p.vals[0], p.vals[1], pp->mpar_loc, 0, 5, g.st));
+    if (std::max(b4, b5) > p.cub_bytes) { cudaFree(p.cub_tmp); p.cub_bytes = std::max(b4, b5); CK(cudaMalloc(&p.cub_tmp, p.cub_bytes)); }
+  }
   CK(cudaMemcpyAsync(p.cs + p.ncell, &q.npar, sizeof(int), cudaMemcpyHostToDevice, g.st));   // after the memset above, same stream
   CK(cudaStreamSynchronize(g.st));
   p.cur = 0; p.on = true;
@@ -651,14 +693,69 @@ extern "C" int pcb200_particles_get_aux(double *np, double *rhop)
   return PCB200_OK;
 }
 
+extern "C" int pcb200_particles_count(int32_t *npar_loc)
+{
+  if (!g.part.on) return fail(PCB200_ESTATE, "pcb200_particles_count: particles are not initialised");
+  if (npar_loc) *npar_loc = g.part.q.npar;
+  return PCB200_OK;
+}
+
+// migrate_particles (particles_mpicomm.f90:267-696) after the periodic wrap: leavers out,
+// holes refilled from the tail, arrivals appended; one small D2H + sync for the new npar_loc
+static int part_migrate()
+{
+  Ctx::Part &p = g.part; PartPar &q = p.q; const MigPar &mg = p.mg;
+  const unsigned nb = (unsigned)std::max(1, (q.npar + 255) / 256);
+  CK(cudaMemsetAsync(p.counters, 0, 64 * sizeof(int), g.st));
+  part_mig_classify<<<nb, 256, 0, g.st>>>(q, mg, p.fp[p.cur], p.slot_of_rank, p.keys[0], p.vals[0], p.leave, p.counters);
+  part_mig_offsets<<<1, 32, 0, g.st>>>(mg, q.npar, p.counters);
+  size_t bytes = p.cub_bytes;
+  CK(cub::DeviceScan::ExclusiveSum(p.cub_tmp, bytes, p.leave, p.pre, q.npar, g.st));
+  bytes = p.cub_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(p.cub_tmp, bytes, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.npar, 0, 5, g.st));
+  const unsigned nbp = (unsigned)std::max(1, (std::max(q.npar, mg.nslots) + 255) / 256);
+  part_mig_pack<<<nbp, 256, 0, g.st>>>(mg, q.npar, q.mpar, p.keys[1], p.vals[1], p.fp[p.cur], p.dfp[p.cur], p.ipar[p.cur], p.counters, p.sendbuf);
+  part_mig_holes<<<nb, 256, 0, g.st>>>(q.npar, p.leave, p.pre, p.counters, p.holes, p.tails);
+  part_mig_fill<<<nb, 256, 0, g.st>>>(q.npar, q.mpar, p.pre, p.counters, p.holes, p.tails, p.fp[p.cur], p.dfp[p.cur], p.ipar[p.cur]);
+  g.launches += 5;
+  CK(cudaGetLastError());
+  const size_t msg = (size_t)MIG_NVAL * mg.cap + 1;
+  NK(g.nccl.GroupStart());
+  for (int s = 0; s < mg.nslots; s++) {
+    NK(g.nccl.Send(p.sendbuf + (size_t)s * msg, msg, 8, p.nbr[s], g.comm, g.st));
+    NK(g.nccl.Recv(p.recvbuf + (size_t)s * msg, msg, 8, p.nbr[s], g.comm, g.st));
+  }
+  NK(g.nccl.GroupEnd());
+  dim3 grd((mg.cap + 255) / 256, mg.nslots);
+  part_mig_append<<<grd, 256, 0, g.st>>>(mg, q.mpar, p.recvbuf, p.counters, p.fp[p.cur], p.dfp[p.cur], p.ipar[p.cur]);
+  g.launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(p.counters_host, p.counters, 64 * sizeof(int), cudaMemcpyDeviceToHost, g.st));
+  CK(cudaStreamSynchronize(g.st));
+  const int err = p.counters_host[29];
+  if (err & 1) return fail(PCB200_EARG, "migrate_particles: a particle wants to migrate to a processor that is not a neighbour");
+  if (err & 2) return fail(PCB200_EARG, "migrate_particles: too many particles migrating (raise PCB200_NPAR_MIG)");
+  if (err & 4) return fail(PCB200_EARG, "migrate_particles: too many particles want to be at this rank (mpar_loc too small)");
+  q.npar = p.counters_host[30];
+  return PCB200_OK;
+}
+
 // particles_timestep_first + particles_boundconds (timestep.f90:127, equ.f90:169)
 static int part_before_rhs(int isub)
 {
-  Ctx::Part &p = g.part; const PartPar &q = p.q; const DevPar &h = g.hp;
-  const unsigned nb = (unsigned)((q.npar + 255) / 256);
+  Ctx::Part &p = g.part; PartPar &q = p.q; const DevPar &h = g.hp;
+  unsigned nb = (unsigned)std::max(1, (q.npar + 255) / 256);
   part_first<<<nb, 256, 0, g.st>>>(p.dfp[p.cur], q.npar, q.mpar, isub == 1 ? 0.0 : g.P.alpha_ts[isub - 1]);
+  g.launches++;
+  if (g.nranks > 1) {
+    part_wrap<<<nb, 256, 0, g.st>>>(q, p.fp[p.cur]);
+    g.launches++;
+    int rcm = part_migrate();
+    if (rcm) return rcm;
+    nb = (unsigned)std::max(1, (q.npar + 255) / 256);
+  }
   part_bc_map<<<nb, 256, 0, g.st>>>(q, p.fp[p.cur], p.inear[p.cur], p.imn_array, p.keys[0], p.vals[0]);
-  g.launches += 2;
+  g.launches++;
   CK(cudaGetLastError());
   size_t bytes = p.cub_bytes;
   CK(cub::DeviceRadixSort::SortPairs(p.cub_tmp, bytes, p.keys[0], p.keys[1], p.vals[0], p.vals[1], q.npar, 0, p.key_bits, g.st));
@@ -678,7 +775,8 @@ static int part_before_rhs(int isub)
   part_invperm<<<nb, 256, 0, g.st>>>(q.npar, p.cvals[1], p.cvals[0]);      // cvals[0] := rank of each particle in its bin list
   g.launches++;
   bytes = p.cub_bytes;
-  // cs[ncell] = npar was set once at initialisation
+  // cs[ncell] = npar (npar changes when particles migrate)
+  if (p.counters) CK(cudaMemcpyAsync(p.cs + p.ncell, p.counters + 30, sizeof(int), cudaMemcpyDeviceToDevice, g.st));
   CK(cub::DeviceScan::ExclusiveSum(p.cub_tmp, bytes, p.ccount, p.cs, p.ncell, g.st));
   (void)h;
   return PCB200_OK;
@@ -689,7 +787,7 @@ static int part_pencils(const double *fin, int ldt)
 {
   Ctx::Part &p = g.part; const PartPar &q = p.q; const pcb200_params &P = g.P;
   if (ldt) CK(cudaMemsetAsync(p.dt1, 0, sizeof(double), g.st));
-  part_drag<<<(unsigned)((q.npar + 127) / 128), 128, 0, g.st>>>(q, fin, p.fp[p.cur], p.dfp[p.cur], p.inear[p.cur], p.cvals[0], p.drag, p.dt1, ldt);
+  part_drag<<<(unsigned)std::max(1, (q.npar + 127) / 128), 128, 0, g.st>>>(q, fin, p.fp[p.cur], p.dfp[p.cur], p.inear[p.cur], p.cvals[0], p.drag, p.dt1, ldt);
   g.launches++;
   if (ldt && q.ldrag_dust) {
     dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
@@ -697,6 +795,46 @@ static int part_pencils(const double *fin, int ldt)
     g.launches++;
   }
   CK(cudaGetLastError());
+  return PCB200_OK;
+}
+
+// fold_df/fold_f between ranks (ghostfold_mpicomm.f90:28-153): the first ghost layer of the
+// deposit sums goes to the neighbour rank and is added to its first interior plane; z, then
+// y, then x; the folded layer is zeroed.  Neighbours are periodic whatever the gas boundary
+// condition is (zlneigh/zuneigh of mpicomm.f90).  acc: [4][mw].
+static int part_fold_exchange(double *acc)
+{
+  Ctx::Part &p = g.part; const pcb200_params &P = g.P; const DevPar &h = g.hp;
+  const int np[3] = {P.nprocx, P.nprocy, P.nprocz}, nloc[3] = {P.nx, P.ny, P.nz};
+  const int ip[3] = {P.ipx, P.ipy, P.ipz};
+  for (int axis = 2; axis >= 0; axis--) {
+    if (np[axis] == 1) continue;
+    auto rank_of = [&](int i) { int q[3] = {ip[0], ip[1], ip[2]}; q[axis] = (i + np[axis]) % np[axis]; return q[0] + np[0] * (q[1] + np[1] * q[2]); };
+    const int nlo = rank_of(ip[axis] - 1), nhi = rank_of(ip[axis] + 1);
+    const long long per = axis == 0 ? (long long)h.my * h.mz : (axis == 1 ? (long long)h.mx * h.mz : (long long)h.mx * h.my);
+    const size_t cnt = (size_t)per * 4;
+    dim3 blk(256), grd((unsigned)((per + 255) / 256), 4);
+    auto copy = [&](double *buf, int plane, int mode) {
+      FaceArgs a; a.f = acc; a.buf = buf; a.axis = axis; a.start = plane; a.unpack = mode; a.nplanes = 1;
+      face_copy<<<grd, blk, 0, g.st>>>(a);
+      g.launches++;
+    };
+    const int n = nloc[axis];
+    copy(p.fold[0], NG - 1, 0);           // my lower ghost layer -> lower neighbour's top interior plane
+    copy(p.fold[1], NG + n, 0);           // my upper ghost layer -> upper neighbour's bottom interior plane
+    NK(g.nccl.GroupStart());
+    NK(g.nccl.Send(p.fold[0], cnt, 8, nlo, g.comm, g.st));
+    NK(g.nccl.Recv(p.fold[3], cnt, 8, nhi, g.comm, g.st));
+    NK(g.nccl.Send(p.fold[1], cnt, 8, nhi, g.comm, g.st));
+    NK(g.nccl.Recv(p.fold[2], cnt, 8, nlo, g.comm, g.st));
+    NK(g.nccl.GroupEnd());
+    copy(p.fold[3], NG + n - 1, 2);       // += upper neighbour's lower ghost layer
+    copy(p.fold[2], NG, 2);               // += lower neighbour's upper ghost layer
+    plane_zero<<<grd, blk, 0, g.st>>>(acc, axis, NG - 1);
+    plane_zero<<<grd, blk, 0, g.st>>>(acc, axis, NG + n);
+    g.launches += 2;
+    CK(cudaGetLastError());
+  }
   return PCB200_OK;
 }
 
@@ -772,8 +910,19 @@ static int do_substep(int isub, int ldiagnos)
     // already produced the new state) f_out; otherwise axpy_update carries it (equ.f90:1046)
     Ctx::Part &pt = g.part;
     dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
-    part_deposit<<<grd, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
-    g.launches++;
+    if (g.nranks == 1) {
+      part_deposit<<<grd, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
+      g.launches++;
+    } else {
+      // split directions deposit into the first ghost layer, which fold_df ships to the neighbour
+      CK(cudaMemsetAsync(pt.acc, 0, (size_t)4 * g.hp.mw * sizeof(double), g.st));
+      dim3 grg((P.nx + 2 + 127) / 128, P.ny + 2, P.nz + 2);
+      part_deposit_ghost<<<grg, blk, 0, g.st>>>(pt.q, pt.drag, pt.cs, pt.acc);
+      g.launches++;
+      if ((rc = part_fold_exchange(pt.acc))) return rc;
+      part_backreact_acc<<<grd, blk, 0, g.st>>>(pt.q, fin, pt.acc, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
+      g.launches++;
+    }
     CK(cudaGetLastError());
   }
   if (auxm > 0) {
@@ -796,7 +945,7 @@ static int do_substep(int isub, int ldiagnos)
     CK(cudaGetLastError());
   }
   if (g.part.on) {
-    part_second<<<(unsigned)((g.part.q.npar + 255) / 256), 256, 0, g.st>>>(g.part.fp[g.part.cur], g.part.dfp[g.part.cur],
+    part_second<<<(unsigned)std::max(1, (g.part.q.npar + 255) / 256), 256, 0, g.st>>>(g.part.fp[g.part.cur], g.part.dfp[g.part.cur],
                                                                          g.part.q.npar, g.part.q.mpar, g.dt_dev, P.beta_ts[isub - 1]);
     g.launches++;
     CK(cudaGetLastError());

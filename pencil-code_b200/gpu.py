@@ -152,4 +152,7 @@ class GPU:
         self._ck(self.lib.pcb200_particles_store(st.fp.ctypes.data, st.dfp.ctypes.data, st.ipar.ctypes.data,
                                                  st.ineargrid.ctypes.data, st.k1_imn.ctypes.data, st.k2_imn.ctypes.data))
         self._ck(self.lib.pcb200_particles_get_aux(st.np_.ctypes.data, st.rhop.ctypes.data))
-        return st
+        n = C.c_int32()
+        self._ck(self.lib.pcb200_particles_count(C.byref(n)))
+        st.npar = n.value                     # changes when particles migrate between ranks
+        return n.value

@@ -158,6 +158,21 @@ def test_unsupported_is_refused(pk, dev):
         dev.initialize_GPU(P, zprof)
 
 
+def test_two_gpu_particles_migrate_and_fold_match_oracle():
+    """2 GPUs split in z, y and x: particle migration (migrate_particles) and the ghost-layer
+    fold of the TSC deposit (fold_df/fold_f) == single-domain oracle, particles matched by ipar"""
+    import os, subprocess, sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29518",
+                        os.path.join(root, "tests", "mgpu_particles_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_two_gpu_halo_exchange_matches_oracle():
     """z-slabs on 2 GPUs (NCCL send/recv halos, allreduce-max dt) == single-domain oracle"""
     import os, subprocess, sys
