@@ -138,12 +138,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--n", type=int, default=512, help="grid points per direction per GPU")
+    ap.add_argument("--n", "--ncell", dest="n", type=int, default=512, help="grid points per direction per GPU (use --ncell under torchrun, whose parser trips over --n)")
     ap.add_argument("--cpu-n", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--particles", type=int, default=0,
-                    help="dust particles per GPU (BASELINE config 5 is 256^3 cells + 1.25e7 particles per GPU); N=1 only")
+                    help="dust particles per GPU (BASELINE config 5 is 256^3 cells + 1.25e7 particles per GPU)")
     ap.add_argument("--decomp", default="", help="nprocx,nprocy,nprocz (default: z-slabs 1,1,N)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -182,8 +182,8 @@ def main():
     dev.register_GPU(f)
     dev.load_farray()
     if args.particles:
-        pp = pk.setups.make_particle_params(P, args.particles, tausp=0.1, eps_dtog=0.5)
-        pst = pk.setups.synthetic_particles(P, pp)
+        pp = pk.setups.make_particle_params(P, args.particles, int(args.particles * 1.25), tausp=0.1, eps_dtog=0.5)
+        pst = pk.setups.synthetic_particles(P, pp, block_only=True)
         dev.particles_initialize(pp)
         dev.particles_load(pst)
 

@@ -275,7 +275,6 @@ contains
       if (lselfgravity) str=trim(str)//', '//'selfgravity'
       if (lsolid_cells) str=trim(str)//', '//'solid_cells'
       if (lspecial) str=trim(str)//', '//'special'
-      if (lparticles .and. ncpus>1) str=trim(str)//', '//'particles on more than one rank'
       if (lparticles_radius.or.lparticles_number.or.lparticles_density.or.lparticles_sink.or. &
           lparticles_selfgravity.or.lparticles_blocks) str=trim(str)//', '//'particle sub-modules'
       if (.not.lcartesian_coords) str=trim(str)//', '//'curvilinear coordinates'

@@ -261,13 +261,20 @@ def make_particle_params(P, npar, mpar=None, *, tausp=0.1, eps_dtog=0.5, backrea
     return pp
 
 
-def synthetic_particles(P, pp, seed=4321, vampl=0.05):
-    """Uniform random positions in the (global) box, small random velocities; ipar = 1..npar."""
-    rng = np.random.default_rng(seed)
+def synthetic_particles(P, pp, seed=4321, vampl=0.05, block_only=False):
+    """Uniform random positions in the global box (or, block_only, in this rank's block),
+    small random velocities; ipar = 1..npar (offset by iproc*npar when block_only)."""
+    iproc = P.ipx + P.nprocx * (P.ipy + P.nprocy * P.ipz)
+    rng = np.random.default_rng(seed + (iproc if block_only else 0))
     st = ParticleState(P, pp.npar_loc, pp.mpar_loc)
     n = pp.npar_loc
+    npr, ip = (P.nprocx, P.nprocy, P.nprocz), (P.ipx, P.ipy, P.ipz)
     for j in range(3):
-        st.fp[j, :n] = P.xyz0[j] + P.Lxyz[j] * rng.random(n)
+        lo, L = P.xyz0[j], P.Lxyz[j]
+        if block_only:
+            L = P.Lxyz[j] / npr[j]
+            lo = P.xyz0[j] + ip[j] * L
+        st.fp[j, :n] = lo + L * rng.random(n)
         st.fp[3 + j, :n] = vampl * rng.standard_normal(n)
-    st.ipar[:n] = np.arange(1, n + 1, dtype=np.int32)
+    st.ipar[:n] = np.arange(1, n + 1, dtype=np.int32) + (iproc * n if block_only else 0)
     return st
