@@ -243,29 +243,39 @@ __global__ void part_dt_cells(PartPar q, const double *__restrict__ f, const int
 __device__ __forceinline__ double part_w(double a)
 { const double b = fabs(a); return b <= 0.5 ? 0.75 - a * a : 1.125 - 1.5 * b + 0.5 * (a * a); }
 
+// GHOST=false: single rank, every direction folds locally; result fused into w / f_out.
+// GHOST=true : some directions are split between ranks; along those the bins of the neighbour
+//   rank are not here, so (as the reference does) the first GHOST LAYER is filled as well and
+//   fold_df/fold_f ships it to the neighbour (ghostfold_mpicomm.f90:46-153).  Threads cover the
+//   interior plus that layer; acc[0] = sum of weights, acc[1..3] = sum of weight*drag (padded grid).
+template <bool GHOST>
 __global__ void __launch_bounds__(128) part_deposit(PartPar q, const double *__restrict__ f, const double *__restrict__ csort,
                                                      const int *__restrict__ cs, double *__restrict__ rhop,
                                                      double *__restrict__ w, double *__restrict__ f_out,
-                                                     const double *__restrict__ dt_dev, double beta)
+                                                     const double *__restrict__ dt_dev, double beta, double *__restrict__ acc)
 {
   const DevPar &c = c_par;
-  const int l = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y, n = blockIdx.z;
-  if (l >= c.nx) return;
+  const int e = GHOST ? 1 : 0;
+  const int l = blockIdx.x * blockDim.x + threadIdx.x - e, m = (int)blockIdx.y - e, n = (int)blockIdx.z - e;
+  if (l >= c.nx + e) return;
+  if (GHOST && ((q.wrap[0] && (l < 0 || l >= c.nx)) || (q.wrap[1] && (m < 0 || m >= c.ny)) || (q.wrap[2] && (n < 0 || n >= c.nz)))) return;
   const size_t M = q.mpar;
   const double xg = q.x0_loc[0] + l * q.h[0];
-  // x bins of the main range and of the wrapped bin (if this cell sits at an x edge)
+  // x bins of the main range and of the wrapped bin (if x folds locally and this cell sits at an x edge)
   const int la = l > 0 ? l - 1 : 0, lb = l < c.nx - 1 ? l + 1 : c.nx - 1;
-  const int lw = l == 0 ? c.nx - 1 : (l == c.nx - 1 ? 0 : -1);
+  const int lw = (GHOST && !q.wrap[0]) ? -1 : (l == 0 ? c.nx - 1 : (l == c.nx - 1 ? 0 : -1));
   const double xgw = l == 0 ? xg + q.Lxyz[0] : xg - q.Lxyz[0];      // image of this point seen from the wrapped bin
   int r0[9], r1[9], w0[9], w1[9];
 #pragma unroll
   for (int j = 0; j < 9; j++) {
     const int oz = j / 3 - 1, oy = j % 3 - 1;
-    int nn = n + oz; nn = nn < 0 ? nn + c.nz : (nn >= c.nz ? nn - c.nz : nn);
-    int mm = m + oy; mm = mm < 0 ? mm + c.ny : (mm >= c.ny ? mm - c.ny : mm);
-    const int row = (nn * c.ny + mm) * c.nx;
-    r0[j] = __ldg(cs + row + la); r1[j] = __ldg(cs + row + lb + 1);
-    w0[j] = lw >= 0 ? __ldg(cs + row + lw) : 0; w1[j] = lw >= 0 ? __ldg(cs + row + lw + 1) : 0;
+    int nn = n + oz, mm = m + oy;
+    bool ok = true;
+    if (nn < 0 || nn >= c.nz) { if (GHOST && !q.wrap[2]) ok = false; else nn = nn < 0 ? nn + c.nz : nn - c.nz; }
+    if (mm < 0 || mm >= c.ny) { if (GHOST && !q.wrap[1]) ok = false; else mm = mm < 0 ? mm + c.ny : mm - c.ny; }
+    const int row = ok ? (nn * c.ny + mm) * c.nx : 0;
+    r0[j] = ok ? __ldg(cs + row + la) : 0; r1[j] = ok ? __ldg(cs + row + lb + 1) : 0;
+    w0[j] = ok && lw >= 0 ? __ldg(cs + row + lw) : 0; w1[j] = ok && lw >= 0 ? __ldg(cs + row + lw + 1) : 0;
   }
   double v0 = 0.0, v1 = 0.0, v2 = 0.0, ws = 0.0;
 #pragma unroll
@@ -287,6 +297,7 @@ __global__ void __launch_bounds__(128) part_deposit(PartPar q, const double *__r
     }
   }
   const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
+  if (GHOST) { acc[i] = ws; acc[c.mw + i] = v0; acc[2 * c.mw + i] = v1; acc[3 * c.mw + i] = v2; return; }
   rhop[i] = ws;
   if (q.ldrag_gas) {
     const double fac = -q.rhop_swarm * exp(-f[(long long)q.ilnrho * c.mw + i]);
@@ -299,50 +310,6 @@ __global__ void __launch_bounds__(128) part_deposit(PartPar q, const double *__r
       if (f_out) f_out[o] += bdt * d[j];
     }
   }
-}
-
-// Multi-rank form of the gather.  Along a direction that is split between ranks the bins of
-// the neighbour rank are not here, so (as the reference does) the particles also deposit into
-// the FIRST GHOST LAYER and fold_df/fold_f ships that layer to the neighbour
-// (ghostfold_mpicomm.f90:46-153).  One thread per cell of the interior plus that layer;
-// acc[0] = sum of weights, acc[1..3] = sum of weight*drag, on the padded grid.
-__global__ void __launch_bounds__(128) part_deposit_ghost(PartPar q, const double *__restrict__ csort, const int *__restrict__ cs,
-                                                           double *__restrict__ acc)
-{
-  const DevPar &c = c_par;
-  const int l = blockIdx.x * blockDim.x + threadIdx.x - 1, m = (int)blockIdx.y - 1, n = (int)blockIdx.z - 1;
-  if (l > c.nx) return;
-  if ((q.wrap[0] && (l < 0 || l >= c.nx)) || (q.wrap[1] && (m < 0 || m >= c.ny)) || (q.wrap[2] && (n < 0 || n >= c.nz))) return;
-  const size_t M = q.mpar;
-  double v0 = 0.0, v1 = 0.0, v2 = 0.0, ws = 0.0;
-#pragma unroll 1
-  for (int oz = -1; oz <= 1; oz++) {
-    int nn = n + oz;
-    if (nn < 0 || nn >= c.nz) { if (!q.wrap[2]) continue; nn = nn < 0 ? nn + c.nz : nn - c.nz; }
-    const double zg = q.x0_loc[2] + (nn - oz) * q.h[2];
-#pragma unroll 1
-    for (int oy = -1; oy <= 1; oy++) {
-      int mm = m + oy;
-      if (mm < 0 || mm >= c.ny) { if (!q.wrap[1]) continue; mm = mm < 0 ? mm + c.ny : mm - c.ny; }
-      const double yg = q.x0_loc[1] + (mm - oy) * q.h[1];
-#pragma unroll 1
-      for (int ox = -1; ox <= 1; ox++) {
-        int ll = l + ox;
-        if (ll < 0 || ll >= c.nx) { if (!q.wrap[0]) continue; ll = ll < 0 ? ll + c.nx : ll - c.nx; }
-        const double xg = q.x0_loc[0] + (ll - ox) * q.h[0];
-        const int id = (nn * c.ny + mm) * c.nx + ll;
-        const int i0 = __ldg(cs + id), i1 = __ldg(cs + id + 1);
-        for (int i = i0; i < i1; i++) {
-          const double wt = (part_w((__ldg(csort + i) - xg) * q.h_1[0]) * part_w((__ldg(csort + M + i) - yg) * q.h_1[1]))
-                            * part_w((__ldg(csort + 2 * M + i) - zg) * q.h_1[2]);
-          ws += wt;
-          if (q.ldrag_gas) { v0 += wt * __ldg(csort + 3 * M + i); v1 += wt * __ldg(csort + 4 * M + i); v2 += wt * __ldg(csort + 5 * M + i); }
-        }
-      }
-    }
-  }
-  const long long i = (long long)(n + NG) * c.sz + (long long)(m + NG) * c.sy + (l + NG);
-  acc[i] = ws; acc[c.mw + i] = v0; acc[2 * c.mw + i] = v1; acc[3 * c.mw + i] = v2;
 }
 
 // after the fold: rhop and the back-reaction from the accumulated sums (interior cells)

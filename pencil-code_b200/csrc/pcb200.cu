@@ -911,13 +911,13 @@ static int do_substep(int isub, int ldiagnos)
     Ctx::Part &pt = g.part;
     dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
     if (g.nranks == 1) {
-      part_deposit<<<grd, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
+      part_deposit<false><<<grd, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta, nullptr);
       g.launches++;
     } else {
       // split directions deposit into the first ghost layer, which fold_df ships to the neighbour
       CK(cudaMemsetAsync(pt.acc, 0, (size_t)4 * g.hp.mw * sizeof(double), g.st));
       dim3 grg((P.nx + 2 + 127) / 128, P.ny + 2, P.nz + 2);
-      part_deposit_ghost<<<grg, blk, 0, g.st>>>(pt.q, pt.drag, pt.cs, pt.acc);
+      part_deposit<true><<<grg, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, nullptr, nullptr, nullptr, g.dt_dev, 0.0, pt.acc);
       g.launches++;
       if ((rc = part_fold_exchange(pt.acc))) return rc;
       part_backreact_acc<<<grd, blk, 0, g.st>>>(pt.q, fin, pt.acc, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
