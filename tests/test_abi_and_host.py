@@ -101,3 +101,83 @@ sys.exit(0 if int(t[0]) else 1)
                         "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_particle_struct_layout_matches_c(pk, tmp_path):
+    src = tmp_path / "szp.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "pcb200.h"\nint main(){printf("%zu %zu %zu\\n",'
+                   'sizeof(pcb200_particle_params),offsetof(pcb200_particle_params,tausp),'
+                   'offsetof(pcb200_particle_params,cdtp_drag));return 0;}\n')
+    exe = tmp_path / "szp"
+    subprocess.check_call(["/usr/bin/gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = [int(v) for v in subprocess.check_output([str(exe)]).split()]
+    PP = pk.abi.ParticleParams
+    assert got == [C.sizeof(PP), PP.tausp.offset, PP.cdtp_drag.offset]
+
+
+def test_block_decomposition_tiles_the_global_grid(pk):
+    """nprocx x nprocy x nprocz blocks with the reference's rank layout
+    iproc = ipx + nprocx*(ipy + nprocy*ipz) (mpicomm.f90:367-369) reproduce the global fields."""
+    Pg, _, gg = pk.setups.make_params(16, 24, 32, magnetic=True)
+    fg = pk.setups.synthetic_fields(Pg, gg)
+    nproc = (2, 3, 2)
+    seen = np.zeros((32, 24, 16), dtype=int)
+    for iproc in range(12):
+        P, _, gl = pk.setups.make_params(16, 24, 32, magnetic=True, nproc=nproc, iproc=iproc)
+        assert (P.nx, P.ny, P.nz) == (8, 8, 16)
+        assert P.ipx + P.nprocx * (P.ipy + P.nprocy * P.ipz) == iproc
+        fl = pk.setups.synthetic_fields(P, gl)
+        sl = (slice(None), slice(P.ipz * 16, P.ipz * 16 + 22), slice(P.ipy * 8, P.ipy * 8 + 14), slice(P.ipx * 8, P.ipx * 8 + 14))
+        assert np.allclose(fl, fg[sl], atol=1e-14)
+        seen[P.ipz * 16:(P.ipz + 1) * 16, P.ipy * 8:(P.ipy + 1) * 8, P.ipx * 8:(P.ipx + 1) * 8] += 1
+    assert (seen == 1).all()
+
+
+def test_four_rank_gloo_xyz_exchange_fills_edges_and_corners(pk, tmp_path):
+    """world_size-4 gloo run (2x2x1 blocks) of the ghost-zone rule of do_substep()/exchange_packed():
+    axis by axis x -> y -> z, each face over the FULL ghost-inclusive extent of the other axes,
+    with the periodic neighbour rule of neighbours() -- reproduces every ghost cell, edges and
+    corners included, without corner messages."""
+    script = tmp_path / "w4.py"
+    script.write_text(f"""
+import os, sys
+sys.path.insert(0, {ROOT!r})
+import numpy as np, torch, torch.distributed as dist
+import __graft_entry__ as g
+pk = g.package()
+rank = int(os.environ['RANK']); world = int(os.environ['WORLD_SIZE'])
+dist.init_process_group('gloo', rank=rank, world_size=world)
+nproc = (2, 2, 1)
+P, _, grid = pk.setups.make_params(16, 16, 8, magnetic=True, nproc=nproc, iproc=rank)
+f = pk.setups.synthetic_fields(P, grid)          # analytic field: ghosts already hold the periodic images
+ref = f.copy()
+f[:, :3] = 0; f[:, -3:] = 0; f[:, :, :3] = 0; f[:, :, -3:] = 0; f[:, :, :, :3] = 0; f[:, :, :, -3:] = 0
+ip = [P.ipx, P.ipy, P.ipz]
+def rank_of(axis, i):
+    q = list(ip); q[axis] = i % nproc[axis]
+    return q[0] + nproc[0] * (q[1] + nproc[1] * q[2])
+for axis in (0, 1, 2):                           # x -> y -> z
+    ax = 3 - axis                                # numpy axis of f(mvar, mz, my, mx)
+    n = f.shape[ax] - 6
+    take = lambda a, b: np.ascontiguousarray(np.take(f, range(a, b), axis=ax))
+    def put(a, vals):
+        idx = [slice(None)] * 4; idx[ax] = slice(a, a + 3); f[tuple(idx)] = vals
+    if nproc[axis] == 1:                         # wraps inside the rank
+        put(0, take(n, n + 3)); put(n + 3, take(3, 6))
+        continue
+    lo, hi = rank_of(axis, ip[axis] - 1), rank_of(axis, ip[axis] + 1)
+    s_lo, s_hi = torch.from_numpy(take(3, 6)), torch.from_numpy(take(n, n + 3))
+    r_hi, r_lo = torch.zeros_like(s_lo), torch.zeros_like(s_hi)
+    reqs = [dist.isend(s_lo, lo, tag=10 + axis), dist.irecv(r_hi, hi, tag=10 + axis),
+            dist.isend(s_hi, hi, tag=20 + axis), dist.irecv(r_lo, lo, tag=20 + axis)]
+    for r in reqs: r.wait()
+    put(n + 3, r_hi.numpy()); put(0, r_lo.numpy())
+ok = np.allclose(f, ref, atol=1e-14)
+t = torch.tensor([1 if ok else 0]); dist.all_reduce(t, op=dist.ReduceOp.MIN)
+dist.destroy_process_group()
+sys.exit(0 if int(t[0]) else 1)
+""")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "4",
+                        "--master-addr", "127.0.0.1", "--master-port", "29534", str(script)],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
