@@ -248,7 +248,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   {
     const int tiles = ((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY);
     int zc = P.nz;
-    while (zc > 32 && tiles * ((P.nz + zc - 1) / zc) < 148 * 4) zc = (zc + 1) / 2;
+    while (zc > 32 && tiles * ((P.nz + zc - 1) / zc) < 148 * 12) zc = (zc + 1) / 2;
     const char *e = getenv("PCB200_ZCHUNK");
     if (e && atoi(e) > 0) zc = atoi(e);
     g.zchunk = zc;
