@@ -144,6 +144,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--particles", type=int, default=0,
                     help="dust particles per GPU (BASELINE config 5 is 256^3 cells + 1.25e7 particles per GPU)")
+    ap.add_argument("--entropy", action="store_true", help="BASELINE config 4 physics: MHD + entropy (chi-const), mvar=8")
     ap.add_argument("--decomp", default="", help="nprocx,nprocy,nprocz (default: z-slabs 1,1,N)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -175,8 +176,10 @@ def main():
     L = 2 * np.pi
     nproc = tuple(int(v) for v in args.decomp.split(",")) if args.decomp else (1, 1, world)
     assert nproc[0] * nproc[1] * nproc[2] == world, "--decomp does not multiply to the world size"
+    extra = dict(entropy=True, chi=1e-4, iheatcond=pk.abi.HCOND["chi-const"]) if args.entropy else {}
     P, zprof, grid = pk.setups.make_params(n * nproc[0], n * nproc[1], n * nproc[2], magnetic=True, nproc=nproc, iproc=rank,
-                                           Lxyz=(L * nproc[0], L * nproc[1], L * nproc[2]), nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3)
+                                           Lxyz=(L * nproc[0], L * nproc[1], L * nproc[2]), nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3,
+                                           **extra)
     f = pk.setups.synthetic_fields(P, grid)
     dev.initialize_GPU(P, zprof)
     dev.register_GPU(f)
@@ -258,11 +261,12 @@ def main():
         "metric": "Mcell-updates/s per RK3 substep", "value": value, "unit": "Mcell-updates/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"isothermal helical-MHD box (BASELINE config 3), {n}^3 cells per GPU, mvar=7",
+        "config": {"workload": (f"MHD + entropy box (BASELINE config 4 physics), {n}^3 cells per GPU, mvar=8" if args.entropy else
+                                f"isothermal helical-MHD box (BASELINE config 3), {n}^3 cells per GPU, mvar=7"),
                    "global_grid": [n * nproc[0], n * nproc[1], n * nproc[2]], "decomposition": list(nproc), "step": "one RK3 time step = 3 substeps incl. BCs, CFL dt, 2N update",
                    "particles_per_gpu": args.particles, "l2": f"inputs larger than L2 ({f.nbytes / 1e9:.2f} GB per buffer)", "dt": dt},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if ach else None,
-                     "traffic": traffic, "peak_source": peak_src, "kernel": "rhs_tma<MAG=1,ENT=0>", "launches_timed": kcount,
+                     "traffic": traffic, "peak_source": peak_src, "kernel": "rhs_tma<MAG=1,ENT=%d>" % int(args.entropy), "launches_timed": kcount,
                      "avg_launch_ms": kms, "kernel_ms_per_substep": ksub, "algorithmic_bytes_per_cell": b_alg,
                      "step_frac": cells_local * b_alg * 3 / (ms / args.steps * 1e-3) / 1e9 / peak,
                      # with ldt the f write of substep 1 is done by axpy_update, not by this kernel:

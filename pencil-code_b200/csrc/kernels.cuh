@@ -562,6 +562,9 @@ __global__ void bc_periodic(BcPerArgs b)
 // ------------------------------------------------------------------------
 #include <cuda.h>
 
+#ifndef PCB200_WPF
+#define PCB200_WPF true
+#endif
 #define PEP 544                 // plane tile padded to a multiple of 128 B (TMA smem alignment)
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -644,6 +647,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
   double *redsm = plain + (size_t)NPF * 2 * PEP;
   unsigned long long *bar = reinterpret_cast<unsigned long long *>(redsm + 8 * NRED);
   constexpr unsigned BOX_BYTES = PE * 8;
+  constexpr bool WPF = PCB200_WPF;     // old 2N register: L2 prefetch + late load instead of an early load held in registers
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx;
   const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
@@ -739,7 +743,8 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
 #pragma unroll
       for (int r = 0; r < NROLE; r++) {
         if (!role_present<MAG, ENT>(r)) continue;
-        wold[r] = __ldcs(a.w + idx + c.foff[r]);
+        if (WPF) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.w + idx + c.foff[r]));
+        else wold[r] = __ldcs(a.w + idx + c.foff[r]);
       }
     }
     // 2. the cell of plane n
@@ -750,6 +755,13 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
     CellAux aux;
     rhs_cell<MAG, ENT, (AUXM > 0)>(acc, c, n, rhs, aux);
     if (tid == 0 && !issued) { mbar_wait(empty, (unsigned)((q0 - 1) & 1)); issue(n, q0); }
+    if (RW && WPF) {      // the lines were prefetched into L2 before the stencils: no registers held across them
+#pragma unroll
+      for (int r = 0; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        wold[r] = __ldcs(a.w + idx + c.foff[r]);
+      }
+    }
     // 3. 2N-RK3 update (timestep.f90:119-122,162-163); f_in(cell) is the window centre
 #pragma unroll
     for (int r = 0; r < NROLE; r++) {
