@@ -563,7 +563,7 @@ __global__ void bc_periodic(BcPerArgs b)
 #include <cuda.h>
 
 #ifndef PCB200_WPF
-#define PCB200_WPF true
+#define PCB200_WPF (MAG && ENT)
 #endif
 #define PEP 544                 // plane tile padded to a multiple of 128 B (TMA smem alignment)
 
