@@ -6,6 +6,7 @@
 //   -> (substep 1 with ldt) max-reduction -> dt -> streaming update.
 // No CPU fallback: every entry point fails loudly without a CUDA device.
 #include "kernels.cuh"
+#include "rhs_dly.cuh"
 #include "particles.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -63,7 +64,9 @@ struct Ctx {
   double diag[PCB200_NDIAG];
   bool use_global = false;      // PCB200_KERNEL=global
   bool use_cpasync = false;     // PCB200_KERNEL=cpasync: cp.async staging instead of TMA
+  bool use_dly = true;          // rhs_dly (delayed z-mixed terms, tensor-memory history); PCB200_KERNEL=tma selects rhs_tma
   int zchunk = 0;
+  int zchunk_dly = 0;           // rhs_dly pays 6 extra steps per chunk: fewer, longer chunks
   int64_t launches = 0;
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
   // multi-GPU
@@ -126,6 +129,7 @@ extern "C" int pcb200_init(int local_rank)
     const char *k = getenv("PCB200_KERNEL");
     g.use_global = k && !strcmp(k, "global");
     g.use_cpasync = k && !strcmp(k, "cpasync");
+    g.use_dly = !k || !strcmp(k, "dly");
     const char *t = getenv("PCB200_TIME_RHS");
     g.time_rhs = t && atoi(t) != 0;
     g.inited = true;
@@ -252,9 +256,21 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
     const char *e = getenv("PCB200_ZCHUNK");
     if (e && atoi(e) > 0) zc = atoi(e);
     g.zchunk = zc;
+    // rhs_dly: one CTA per SM, a chunk of zc planes takes zc+6 steps (+ ~6 steps of start-up latency);
+    // pick the chunk length that minimises waves x steps
+    int best = P.nz; double bestc = 1e30;
+    for (int nch = 1; nch <= 64 && (P.nz + nch - 1) / nch >= 16; nch++) {
+      const int z = (P.nz + nch - 1) / nch;
+      const double waves = ceil((double)tiles * nch / 148.0);
+      const double cost = waves * (z + 12);
+      if (cost < bestc * 0.999) { bestc = cost; best = z; }
+    }
+    if (e && atoi(e) > 0) best = atoi(e);
+    g.zchunk_dly = best;
   }
   {
-    const size_t nb_m = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + g.zchunk - 1) / g.zchunk + 2);
+    const int zcmin = g.zchunk < g.zchunk_dly ? g.zchunk : g.zchunk_dly;
+    const size_t nb_m = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + zcmin - 1) / zcmin + 2);
     const size_t nb_g = (size_t)((P.nx + 31) / 32) * ((P.ny + 3) / 4) * ((P.nz + 1) / 2 + 2);
     const size_t need = (nb_m > nb_g ? nb_m : nb_g) * NRED;
     if (need > g.npartials) { if (g.partials) cudaFree(g.partials); CK(cudaMalloc(&g.partials, need * sizeof(double))); g.npartials = need; }
@@ -273,6 +289,11 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   OPTINT4(false, false); OPTINT4(true, false); OPTINT4(false, true); OPTINT4(true, true);
 #undef OPTINT4
 #undef OPTINT
+#define OPTIND(M, E) CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
+                     CK(cudaFuncSetAttribute(rhs_dly<M, E, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
+                     CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM))
+  OPTIND(false, false); OPTIND(true, false);
+#undef OPTIND
   CK(cudaStreamSynchronize(g.st));
   g.have_par = true;
   return PCB200_OK;
@@ -484,6 +505,17 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     *nblocks_out = grd.x * grd.y * grd.z;
     const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
     const bool rw = a.alpha != 0.0;
+    if (g.use_dly && P.lbidiagonal_derij && AUXM < 2 && !E) {
+      a.zchunk = g.zchunk_dly < (z_hi - z_lo) ? g.zchunk_dly : (z_hi - z_lo);
+      grd.z = (z_hi - z_lo + a.zchunk - 1) / a.zchunk;
+      *nblocks_out = grd.x * grd.y * grd.z;
+      // centre-plane-only stencils, z-mixed terms finished three planes late from tensor memory
+      constexpr int AX = AUXM < 2 ? AUXM : 0;
+      if (M) { if (rw) rhs_dly<true, false, 0, true><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm);
+               else    rhs_dly<true, false, AX, false><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm); }
+      else   { if (rw) rhs_dly<false, false, 0, true><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm);
+               else    rhs_dly<false, false, AX, false><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm); }
+    } else {
     // the old 2N register is only read on substeps 2,3, which never need the reductions
 #define LT(M, E) do { if (P.lbidiagonal_derij) { \
                         if (rw) rhs_tma<M, E, 0, true, true><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); \
@@ -493,6 +525,7 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
                         else    rhs_tma<M, E, AUXM, false, false><<<grd, blk, TmaCfg<M, E>::SMEM, g.st>>>(a, tm); } } while (0)
     if (M && E) LT(true, true); else if (M) LT(true, false); else if (E) LT(false, true); else LT(false, false);
 #undef LT
+    }
   } else {
     a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
     dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);

@@ -87,6 +87,7 @@ struct MagOut {
   double j2;             // for Ohmic heating (magnetic.f90:5127)
   double advec_va2;      // Alfven CFL term (magnetic.f90:5438)
   double b2, ab, jb;     // diagnostics
+  double bx, by, bz;     // B itself (rhs_dly finishes the Lorentz force three planes late)
 };
 
 // ---------------- magnetic (magnetic.f90:3587-3990, 4229-5589) ----------------
@@ -107,6 +108,7 @@ PC_DEV void mag_part(const A &a, const DevPar &c, double ux, double uy, double u
   const double jx = c.mu01 * ((dxy<R_AY>(a, c.fxy) - axyy) - (axzz - dxz<R_AZ>(a, c.fzx)));
   const double jy = c.mu01 * ((dyz<R_AZ>(a, c.fyz) - ayzz) - (ayxx - dxy<R_AX>(a, c.fxy)));
   const double jz = c.mu01 * ((dxz<R_AX>(a, c.fzx) - azxx) - (azyy - dyz<R_AY>(a, c.fyz)));
+  m.bx = bx; m.by = by; m.bz = bz;
   m.j2 = jx * jx + jy * jy + jz * jz;
   m.fx = rho1 * (jy * bz - jz * by);
   m.fy = rho1 * (jz * bx - jx * bz);

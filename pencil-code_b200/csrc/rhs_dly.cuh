@@ -1,0 +1,341 @@
+// rhs_dly.cuh -- z-marching kernel with delayed z-mixed derivatives (sm_100a).
+//
+// rhs_tma spends 96 of its 234 shared-memory loads per cell on the xz/yz
+// bidiagonal mixed derivatives (derij_main, deriv.f90:1385-1423):
+//     d2g/dxdz (z) = fzx * sum_k c_k [ D_k(z+k) - D_k(z-k) ],   D_k(z') = g(x+k,y,z') - g(x-k,y,z')
+// D_k(z') is exactly the difference the thread forms anyway for dg/dx on the
+// plane z'.  This kernel therefore never loads a neighbour outside the centre
+// plane: it keeps the (pre-scaled) D_k of the last six planes in a per-thread
+// history in TENSOR MEMORY (tcgen05.st / tcgen05.ld, 32x32b: lane = thread,
+// columns = private scratch, 128 doubles per thread) and completes the terms
+// that need the z-mixed derivatives three planes late.  Those terms enter the
+// right-hand side linearly:
+//     du/dt  += nu/3 * (z-mixed part of grad div u)              (viscosity.f90:1421-1448)
+//     du/dt  += rho1 * (Jm x B),  Jm = z-mixed part of J         (magnetic.f90:3787,4360)
+// so step p computes everything else of plane p ("phase A", u-part parked in
+// TMEM together with rho1*B) and finishes du/dt of plane p-3 ("phase B").
+// Shared memory holds 6 slots per field (centre .. centre+4 for the thread's
+// own z-column, +1 in flight) for all fields instead of 8 for six of them.
+//
+// Available for lbidiagonal_derij=T, AUXM<2 (the full 0-D diagnostics need |J|^2 at the
+// centre plane: those substeps use rhs_tma) and, with magnetic+entropy, lohmic_heat=F.
+#pragma once
+#include "kernels.cuh"
+#include <type_traits>
+
+#define NSD 6                  // ring slots per field: centre .. centre+4 landed, centre+5 in flight
+
+// ---- tensor memory as per-thread scratch ----------------------------------
+PC_DEV void tm_st2(unsigned ta, double a)
+{ asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(ta), "r"(__double2loint(a)), "r"(__double2hiint(a))); }
+PC_DEV void tm_st4(unsigned ta, double a, double b)
+{ asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ta), "r"(__double2loint(a)), "r"(__double2hiint(a)),
+               "r"(__double2loint(b)), "r"(__double2hiint(b))); }
+PC_DEV void tm_st8(unsigned ta, double a, double b, double c, double d)
+{ asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(ta),
+               "r"(__double2loint(a)), "r"(__double2hiint(a)), "r"(__double2loint(b)), "r"(__double2hiint(b)),
+               "r"(__double2loint(c)), "r"(__double2hiint(c)), "r"(__double2loint(d)), "r"(__double2hiint(d))); }
+PC_DEV void tm_ld2(unsigned ta, unsigned *r)
+{ asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(ta)); }
+PC_DEV void tm_ld4(unsigned ta, unsigned *r)
+{ asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(ta)); }
+PC_DEV void tm_ld8(unsigned ta, unsigned *r)
+{ asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(ta)); }
+PC_DEV void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+PC_DEV void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// Group g (0..NGRP-1) of NC doubles (NC = 3 or 6) of this thread.  Every access is naturally
+// aligned: the first 2/3 of a group lives in region A (units of UA columns), the rest in
+// region B (units of UA/2 columns) behind it.
+#define DLY_NGRP 21            // history D1: 5 slots (groups 0-4), D2: 6 (5-10), D3: 7 (11-17); pending: 3 (18-20)
+template <int NC> PC_DEV void tm_st_group(unsigned t0, int g, const double *v)
+{
+  if (NC == 6) { tm_st8(t0 + g * 8, v[0], v[1], v[2], v[3]); tm_st4(t0 + DLY_NGRP * 8 + g * 4, v[4], v[5]); }
+  else         { tm_st4(t0 + g * 4, v[0], v[1]); tm_st2(t0 + DLY_NGRP * 4 + g * 2, v[2]); }
+}
+template <int NC> PC_DEV void tm_ld_group(unsigned t0, int g, unsigned *r)   // r[2*NC]; valid after tm_wait_ld()
+{
+  if (NC == 6) { tm_ld8(t0 + g * 8, r); tm_ld4(t0 + DLY_NGRP * 8 + g * 4, r + 8); }
+  else         { tm_ld4(t0 + g * 4, r); tm_ld2(t0 + DLY_NGRP * 4 + g * 2, r + 4); }
+}
+PC_DEV double tm_dbl(const unsigned *r, int i) { return __hiloint2double((int)r[2 * i + 1], (int)r[2 * i]); }
+
+// ring position of a role (absent roles are compacted away)
+template <bool MAG, bool ENT> PC_DEV constexpr int dly_fidx(int R)
+{ return R < 3 ? R : (R < 6 ? R : (R == R_LNRHO ? (MAG ? 6 : 3) : (MAG ? 7 : 4))); }
+
+template <bool MAG, bool ENT> struct DlyCfg {
+  static constexpr int NF = 4 + (MAG ? 3 : 0) + (ENT ? 1 : 0);
+  static constexpr int NC = MAG ? 6 : 3;                      // z-mixed combinations kept per plane and distance k
+  static constexpr int NDBL = NF * NSD * PEP;
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + 8 * NRED + 6) + 128;
+  // tensor-memory groups per thread (NC doubles each), see DLY_NGRP
+  static_assert(DLY_NGRP * NC * 2 <= 256, "tensor-memory budget per thread");
+};
+
+// centre-plane accessor: x/y neighbours from the ring slot of the centre plane, z from the
+// register window; the z-mixed accessors return 0 (those terms are completed in phase B)
+template <bool MAG, bool ENT>
+struct DlyAcc {
+  PC_DEV constexpr bool bidiag() const { return true; }
+  const double *smem0;
+  unsigned cb;            // byte offset of this thread's cell in the ring slot of the centre plane
+  double w[NROLE][7];     // own column, planes z-3..z+3
+  template <int R, int OFF> PC_DEV double cenv() const { return lds_at(smem0, cb, dly_fidx<MAG, ENT>(R) * NSD * PEP + OFF); }
+  template <int R> PC_DEV double c() const { return w[R][3]; }
+  template <int R, int K> PC_DEV double x() const { return cenv<R, K>(); }
+  template <int R, int K> PC_DEV double y() const { return cenv<R, K * HX>(); }
+  template <int R, int K> PC_DEV double z() const { return w[R][3 + K]; }
+  template <int R, int KX, int KY> PC_DEV double xy() const { return cenv<R, KX + KY * HX>(); }
+  template <int R, int KX, int KZ> PC_DEV double xz() const { return 0.0; }
+  template <int R, int KY, int KZ> PC_DEV double yz() const { return 0.0; }
+  template <int R, int K> PC_DEV double dx() const { return cenv<R, K>() - cenv<R, -K>(); }
+  template <int R, int K> PC_DEV double dy() const { return cenv<R, K * HX>() - cenv<R, -K * HX>(); }
+};
+
+// the NC pre-scaled combinations of distance K on the centre plane
+template <bool MAG, bool ENT, int K>
+PC_DEV void dly_combos(const DlyAcc<MAG, ENT> &a, const DevPar &c, double *__restrict__ d)
+{
+  const double ck = K == 1 ? 270.0 : (K == 2 ? -27.0 : 2.0);
+  const double third = 1.0 / 3.0;
+  const double sx = ck * c.fzx, sy = ck * c.fyz;
+  const double vu = c.nu * third;
+  d[0] = (vu * sx) * a.template dx<R_UZ, K>();                                   // nu/3 dxz(uz)
+  d[1] = (vu * sy) * a.template dy<R_UZ, K>();                                   // nu/3 dyz(uz)
+  d[2] = vu * (sx * a.template dx<R_UX, K>() + sy * a.template dy<R_UY, K>());   // nu/3 (dxz(ux) + dyz(uy))
+  if (MAG) {
+    d[3] = (c.mu01 * sx) * a.template dx<R_AZ, K>();                             // Jm_x = mu01 dxz(Az)
+    d[4] = (c.mu01 * sy) * a.template dy<R_AZ, K>();                             // Jm_y = mu01 dyz(Az)
+    d[5] = c.mu01 * (sx * a.template dx<R_AX, K>() + sy * a.template dy<R_AY, K>());   // Jm_z
+  }
+}
+
+template <bool MAG, bool ENT, int AUXM, bool RW>
+__global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_constant__ CUtensorMap tmap)
+{
+  static_assert(AUXM < 2, "full diagnostics run through rhs_tma");
+  typedef DlyCfg<MAG, ENT> Cfg;
+  constexpr int NC = Cfg::NC, NF = Cfg::NF;
+  const DevPar &c = c_par;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *smem = reinterpret_cast<double *>(smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u));
+  double *ring = smem;
+  double *redsm = smem + (size_t)Cfg::NDBL;
+  unsigned long long *bar = reinterpret_cast<unsigned long long *>(redsm + 8 * NRED);
+  unsigned *tbase_sm = reinterpret_cast<unsigned *>(bar + 4);
+  constexpr unsigned BOX_BYTES = PE * 8;
+
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx, warp = tid >> 5;
+  const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
+  const int zb = a.z_lo + blockIdx.z * a.zchunk;
+  const int ze = min(zb + a.zchunk, a.z_hi);
+  const int nzc = ze - zb;
+  const int nstep = nzc + 6;                  // centre planes zb-3 .. ze+2 (ring planes 0 .. nzc+5)
+  const bool active = (x0 + tx < c.nx) && (y0 + ty < c.ny);
+  const int lx = min(x0 + tx, c.nx - 1), ly = min(y0 + ty, c.ny - 1);
+  const long long col = (long long)(ly + NG) * c.sy + (lx + NG);
+  const int tb = (ty + NG) * HX + tx + NG;
+  const bool ww = a.write_w != 0 && active, wf = a.write_f != 0 && active;
+
+  // full[b]: ring plane q >= 4 completes phase (q-4)/2 of full[q&1] (prologue planes 0..4: phase 0 of
+  // full[0]); two barriers because plane q+1 is armed while plane q may still be in flight.
+  // empty[s&1]: phase s/2 completes when all NTHR threads are done with step s (warps drift up to
+  // two steps apart, so consecutive steps must not share a barrier).
+  unsigned long long *full = bar, *empty = bar + 2;
+  if (tid == 0) {
+    mbar_init(full, 1);
+    mbar_init(full + 1, 1);
+    mbar_init(empty, NTHR);
+    mbar_init(empty + 1, NTHR);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_sm)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  // this warp's lane quarter; warps 4..7 use the upper 256 columns
+  const unsigned t0 = *tbase_sm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * 256);
+
+  auto issue_plane = [&](int q, int sl) __attribute__((always_inline)) {     // ring plane q (padded z = zb+q) of every field into slot sl = q % NSD
+    unsigned long long *fb = full + (q >= 4 ? (q & 1) : 0);
+#pragma unroll
+    for (int r = 0; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+      tma_load_3d(ring + ((size_t)dly_fidx<MAG, ENT>(r) * NSD + sl) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + q, fb);
+    }
+  };
+  if (tid == 0) {
+    mbar_expect_tx(full, (unsigned)(NF * 5 * BOX_BYTES));
+#pragma unroll 1
+    for (int q = 0; q < 5; q++) issue_plane(q, q);
+  }
+  // zero the history and the pending slots (defined values in the first steps)
+  {
+    double z6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll 1
+    for (int g = 0; g < DLY_NGRP; g++) tm_st_group<NC>(t0, g, z6);
+  }
+  DlyAcc<MAG, ENT> acc;
+  acc.smem0 = smem;
+#pragma unroll
+  for (int r = 0; r < NROLE; r++)
+#pragma unroll
+    for (int k = 0; k < 7; k++) acc.w[r][k] = 0.0;
+  double red[NRED];
+#pragma unroll
+  for (int q = 0; q < NRED; q++) red[q] = 0.0;
+  const double beta_dt = a.write_f ? a.beta * a.dt_dev[0] : 0.0;
+  mbar_wait(full, 0);
+  // window of step 0: centre = ring plane 0, planes 0..3 are in the ring
+#pragma unroll
+  for (int r = 0; r < NROLE; r++) {
+    if (!role_present<MAG, ENT>(r)) continue;
+#pragma unroll
+    for (int k = 0; k < 4; k++) acc.w[r][3 + k] = ring[((size_t)dly_fidx<MAG, ENT>(r) * NSD + k) * PEP + tb];
+  }
+
+  int c5 = 0, c6 = 0, c7 = 0, c3 = 0;         // s % 5, s % 6, s % 7, s % 3
+  // one step; FULL: centre plane and plane n-3 both inside the chunk (no masks)
+  auto step = [&](const int s, auto full_tag) __attribute__((always_inline)) {
+    constexpr bool FULL = decltype(full_tag)::value;
+    const int n = zb - NG + s;                // centre plane, interior-relative
+    const bool more = s + 5 < nstep;          // ring plane s+5 exists: issue it into the slot of plane s-1
+    bool issued = true;
+    if (more && tid == 0) {
+      issued = s == 0 || mbar_test_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
+      if (issued) { mbar_expect_tx(full + ((s + 1) & 1), (unsigned)(NF * BOX_BYTES)); issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1); }
+    }
+    const bool doA = FULL || (s >= 3 && s < nzc + 3);   // phase A produces output (centre plane inside the chunk)
+    const bool doB = FULL || s >= 6;                    // phase B finishes plane n-3
+    const long long idx = (long long)(n + NG) * c.sz + col;
+    const long long idxB = idx - 3 * c.sz;
+    // old 2N register of the fields that leave in phase A
+    double wold[NROLE];
+    if (RW) {
+#pragma unroll
+      for (int r = 3; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        wold[r] = __ldcs(a.w + idx + c.foff[r]);
+      }
+    }
+    // ---- phase A: everything of plane n except the z-mixed terms ----
+    acc.cb = (unsigned)((c6 * PEP + tb) * 8);
+    // the pre-scaled x/y differences go to the history at once (slots that are not read in this step)
+    {
+      double d[6];
+      dly_combos<MAG, ENT, 1>(acc, c, d);
+      tm_st_group<NC>(t0, c5, d);
+      dly_combos<MAG, ENT, 2>(acc, c, d);
+      tm_st_group<NC>(t0, 5 + c6, d);
+    }
+    double d3[6];
+    dly_combos<MAG, ENT, 3>(acc, c, d3);
+    tm_st_group<NC>(t0, 11 + c7, d3);
+    double rhs[NROLE];
+    CellAux aux;
+    MagOut m;
+    m.fx = m.fy = m.fz = m.j2 = m.advec_va2 = m.b2 = m.ab = m.jb = 0.0;
+    m.bx = m.by = m.bz = 0.0;
+    const double rho1 = exp(-acc.template c<R_LNRHO>());
+    if (MAG) mag_part<(AUXM > 0)>(acc, c, acc.template c<R_UX>(), acc.template c<R_UY>(), acc.template c<R_UZ>(), rho1, rhs + R_AX, m);
+    HydroPend hp;
+    hydro_pre<MAG, ENT, (AUXM > 0)>(acc, c, FULL ? n : min(max(n, 0), c.nz - 1), rhs, aux, hp);
+    hydro_finish<MAG, ENT, (AUXM > 0)>(c, hp, m, rhs, aux);
+    if (tid == 0 && !issued) {
+      mbar_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
+      mbar_expect_tx(full + ((s + 1) & 1), (unsigned)(NF * BOX_BYTES));
+      issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1);
+    }
+    // ---- phase B: finish du/dt of plane n-3 ----
+    unsigned h3[2 * NC], h2a[2 * NC], h2b[2 * NC], h1a[2 * NC], h1b[2 * NC], pn[2 * NC];
+    tm_wait_st();                                                   // the history stores of step s-1 are visible
+    tm_ld_group<NC>(t0, 11 + (c7 == 6 ? 0 : c7 + 1), h3);           // D3(s-6)
+    tm_ld_group<NC>(t0, 5 + (c6 == 0 ? 5 : c6 - 1), h2a);           // D2(s-1)
+    tm_ld_group<NC>(t0, 5 + (c6 == 5 ? 0 : c6 + 1), h2b);           // D2(s-5)
+    tm_ld_group<NC>(t0, c5 >= 2 ? c5 - 2 : c5 + 3, h1a);            // D1(s-2)
+    tm_ld_group<NC>(t0, c5 == 4 ? 0 : c5 + 1, h1b);                 // D1(s-4)
+    const int pg = 18 + c3;                                         // pending slot of plane s-3 (and of plane s)
+    tm_ld_group<NC>(t0, pg, pn);
+    if (RW) {
+#pragma unroll
+      for (int r = 0; r < 3; r++) wold[r] = __ldcs(a.w + (doB ? idxB : idx) + c.foff[r]);
+    }
+    // fields without z-mixed terms leave while the tensor-memory loads are in flight
+#pragma unroll
+    for (int r = 3; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+      const long long i = idx + c.foff[r];
+      const double wv = RW ? rhs[r] + a.alpha * wold[r] : rhs[r];
+      if (ww && doA) __stcs(a.w + i, wv);
+      if (wf && doA) __stcs(a.f_out + i, acc.w[r][3] + beta_dt * wv);
+    }
+    if (AUXM > 0 && active && doA) red[RD_DT1] = fmax(red[RD_DT1], aux.dt1);
+    tm_wait_ld();
+    {
+      double pv[6];
+      pv[0] = rhs[R_UX]; pv[1] = rhs[R_UY]; pv[2] = rhs[R_UZ];
+      if (MAG) { pv[3] = rho1 * m.bx; pv[4] = rho1 * m.by; pv[5] = rho1 * m.bz; }
+      tm_st_group<NC>(t0, pg, pv);
+    }
+    double mz[6];
+#pragma unroll
+    for (int q = 0; q < NC; q++)
+      mz[q] = (d3[q] - tm_dbl(h3, q)) + (tm_dbl(h2a, q) - tm_dbl(h2b, q)) + (tm_dbl(h1a, q) - tm_dbl(h1b, q));
+    double ru[3];
+    ru[0] = tm_dbl(pn, 0) + mz[0]; ru[1] = tm_dbl(pn, 1) + mz[1]; ru[2] = tm_dbl(pn, 2) + mz[2];
+    if (MAG) {
+      const double qx = tm_dbl(pn, 3), qy = tm_dbl(pn, 4), qz = tm_dbl(pn, 5);      // rho1*B of plane n-3
+      ru[0] += mz[4] * qz - mz[5] * qy;
+      ru[1] += mz[5] * qx - mz[3] * qz;
+      ru[2] += mz[3] * qy - mz[4] * qx;
+    }
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+      const long long i = idxB + c.foff[r];
+      const double wv = RW ? ru[r] + a.alpha * wold[r] : ru[r];
+      if (ww && doB) __stcs(a.w + i, wv);
+      if (wf && doB) __stcs(a.f_out + i, acc.w[r][0] + beta_dt * wv);
+    }
+
+    // ---- next plane: shift the z window, release the centre slot ----
+    if (s + 1 == nstep) return;
+    const bool have4 = s + 4 < nstep;
+    if (have4) mbar_wait(full + (s & 1), (unsigned)((s >> 1) & 1));   // ring plane s+4: phase s/2 of full[s&1]
+    const int nl = c6 >= 2 ? c6 - 2 : c6 + 4;                         // slot of ring plane s+4
+#pragma unroll
+    for (int r = 0; r < NROLE; r++) {
+      if (!role_present<MAG, ENT>(r)) continue;
+#pragma unroll
+      for (int k = 0; k < 6; k++) acc.w[r][k] = acc.w[r][k + 1];
+      acc.w[r][6] = have4 ? ring[((size_t)dly_fidx<MAG, ENT>(r) * NSD + nl) * PEP + tb] : 0.0;
+    }
+    mbar_arrive(empty + (s & 1));
+    c5 = c5 == 4 ? 0 : c5 + 1;
+    c6 = c6 == 5 ? 0 : c6 + 1;
+    c7 = c7 == 6 ? 0 : c7 + 1;
+    c3 = c3 == 2 ? 0 : c3 + 1;
+  };
+  {
+    int s = 0;
+    const int s_main_end = nzc + 3;
+#pragma unroll 1
+    for (; s < 6; s++) step(s, std::false_type());
+#pragma unroll 1
+    for (; s < s_main_end; s++) step(s, std::true_type());
+#pragma unroll 1
+    for (; s < nstep; s++) step(s, std::false_type());
+  }
+  if (AUXM > 0) {
+    const int bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    block_reduce_store<AUXM>(red, tid, NTHR, redsm, a.partials, bl);
+  }
+  tm_wait_st();
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(*tbase_sm), "n"(512) : "memory");
+}
