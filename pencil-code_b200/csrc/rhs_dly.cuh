@@ -69,7 +69,8 @@ template <bool MAG, bool ENT> struct DlyCfg {
   static constexpr int NF = 4 + (MAG ? 3 : 0) + (ENT ? 1 : 0);
   static constexpr int NC = MAG ? 6 : 3;                      // z-mixed combinations kept per plane and distance k
   static constexpr int NDBL = NF * NSD * PEP;
-  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + 8 * NRED + 6) + 128;
+  static constexpr int NWB = 2 * NF * NTHR;                   // old-2N-register staging: [2 steps][field][thread]
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + NWB + 8 * NRED + 6) + 128;
   // tensor-memory groups per thread (NC doubles each), see DLY_NGRP
   static_assert(DLY_NGRP * NC * 2 <= 256, "tensor-memory budget per thread");
 };
@@ -122,7 +123,8 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double *smem = reinterpret_cast<double *>(smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u));
   double *ring = smem;
-  double *redsm = smem + (size_t)Cfg::NDBL;
+  double *wbuf = smem + (size_t)Cfg::NDBL;
+  double *redsm = wbuf + Cfg::NWB;
   unsigned long long *bar = reinterpret_cast<unsigned long long *>(redsm + 8 * NRED);
   unsigned *tbase_sm = reinterpret_cast<unsigned *>(bar + 4);
   constexpr unsigned BOX_BYTES = PE * 8;
@@ -199,6 +201,22 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     for (int k = 0; k < 4; k++) acc.w[r][3 + k] = ring[((size_t)dly_fidx<MAG, ENT>(r) * NSD + k) * PEP + tb];
   }
 
+  // The old 2N register w of step s is staged by cp.async one step ahead into wbuf[s&1][field][tid]
+  // (own cell only: no barrier, no registers held across the stencils).  u belongs to plane n-3.
+  auto stage_w = [&](const int s) __attribute__((always_inline)) {
+    if (RW && s < nstep) {
+      const long long idx = (long long)(zb + s) * c.sz + col;
+      const long long idu = s >= 6 ? idx - 3 * c.sz : idx;
+      double *dst = wbuf + (size_t)(s & 1) * NF * NTHR + tid;
+#pragma unroll
+      for (int r = 0; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        cp_async8(dst + dly_fidx<MAG, ENT>(r) * NTHR, a.w + (r < 3 ? idu : idx) + c.foff[r]);
+      }
+    }
+    if (RW) cp_async_commit();
+  };
+  stage_w(0);
   int c5 = 0, c6 = 0, c7 = 0, c3 = 0;         // s % 5, s % 6, s % 7, s % 3
   // one step; FULL: centre plane and plane n-3 both inside the chunk (no masks)
   auto step = [&](const int s, auto full_tag) __attribute__((always_inline)) {
@@ -214,15 +232,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     const bool doB = FULL || s >= 6;                    // phase B finishes plane n-3
     const long long idx = (long long)(n + NG) * c.sz + col;
     const long long idxB = idx - 3 * c.sz;
-    // old 2N register of the fields that leave in phase A
-    double wold[NROLE];
-    if (RW) {
-#pragma unroll
-      for (int r = 3; r < NROLE; r++) {
-        if (!role_present<MAG, ENT>(r)) continue;
-        wold[r] = __ldcs(a.w + idx + c.foff[r]);
-      }
-    }
+    stage_w(s + 1);
     // ---- phase A: everything of plane n except the z-mixed terms ----
     acc.cb = (unsigned)((c6 * PEP + tb) * 8);
     // the pre-scaled x/y differences go to the history at once (slots that are not read in this step)
@@ -261,9 +271,15 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     tm_ld_group<NC>(t0, c5 == 4 ? 0 : c5 + 1, h1b);                 // D1(s-4)
     const int pg = 18 + c3;                                         // pending slot of plane s-3 (and of plane s)
     tm_ld_group<NC>(t0, pg, pn);
+    double wold[NROLE];
     if (RW) {
+      asm volatile("cp.async.wait_group 1;" ::: "memory");          // this step's group has landed (next step's may be in flight)
+      const double *src = wbuf + (size_t)(s & 1) * NF * NTHR + tid;
 #pragma unroll
-      for (int r = 0; r < 3; r++) wold[r] = __ldcs(a.w + (doB ? idxB : idx) + c.foff[r]);
+      for (int r = 0; r < NROLE; r++) {
+        if (!role_present<MAG, ENT>(r)) continue;
+        wold[r] = src[dly_fidx<MAG, ENT>(r) * NTHR];
+      }
     }
     // fields without z-mixed terms leave while the tensor-memory loads are in flight
 #pragma unroll
