@@ -266,7 +266,7 @@ def main():
                    "global_grid": [n * nproc[0], n * nproc[1], n * nproc[2]], "decomposition": list(nproc), "step": "one RK3 time step = 3 substeps incl. BCs, CFL dt, 2N update",
                    "particles_per_gpu": args.particles, "l2": f"inputs larger than L2 ({f.nbytes / 1e9:.2f} GB per buffer)", "dt": dt},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if ach else None,
-                     "traffic": traffic, "peak_source": peak_src, "kernel": "rhs_tma<MAG=1,ENT=%d>" % int(args.entropy), "launches_timed": kcount,
+                     "traffic": traffic, "peak_source": peak_src, "kernel": "%s<MAG=1,ENT=%d>" % (dev.kernel_name(), int(args.entropy)), "launches_timed": kcount,
                      "avg_launch_ms": kms, "kernel_ms_per_substep": ksub, "algorithmic_bytes_per_cell": b_alg,
                      "step_frac": cells_local * b_alg * 3 / (ms / args.steps * 1e-3) / 1e9 / peak,
                      # with ldt the f write of substep 1 is done by axpy_update, not by this kernel:

@@ -106,6 +106,7 @@ SYMBOLS = {
     "pcb200_particles_store": (C.c_int, [C.c_void_p] * 6),
     "pcb200_particles_get_aux": (C.c_int, [C.c_void_p, C.c_void_p]),
     "pcb200_particles_count": (C.c_int, [C.POINTER(C.c_int32)]),
+    "pcb200_kernel_name": (C.c_char_p, []),
     "pcb200_last_error": (C.c_char_p, []),
     "pcb200_abi_version": (C.c_int, []),
 }

@@ -789,7 +789,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
     for (int r = 0; r < NROLE; r++) {
       if (!role_present<MAG, ENT>(r)) continue;
 #pragma unroll
-      for (int k = 0; k < 6; k++) acc.w[r][k] = acc.w[r][k + 1];
+      for (int k = 0; k < 6; k++) asm volatile("mov.b64 %0, %1;" : "=d"(acc.w[r][k]) : "d"(acc.w[r][k + 1]));   // one move each, in this order
       if (r < 6) acc.w[r][6] = ring[((size_t)r * NSLOT + ((q0 + 7) & (NSLOT - 1))) * PEP + tb];
       else acc.w[r][6] = wnext[r];
     }

@@ -66,6 +66,7 @@ struct Ctx {
   bool use_cpasync = false;     // PCB200_KERNEL=cpasync: cp.async staging instead of TMA
   bool use_dly = true;          // rhs_dly (delayed z-mixed terms, tensor-memory history); PCB200_KERNEL=tma selects rhs_tma
   int zchunk = 0;
+  const char *kname = "";        // kernel of the last substep launch
   int zchunk_dly = 0;           // rhs_dly pays 6 extra steps per chunk: fewer, longer chunks
   int64_t launches = 0;
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
@@ -105,6 +106,7 @@ static int fail(int code, const std::string &msg) { g.err = msg; return code; }
   return fail(PCB200_ENCCL, std::string(#call) + ": " + (g.nccl.GetErrorString ? g.nccl.GetErrorString(r_) : "nccl error")); } while (0)
 
 extern "C" const char *pcb200_last_error(void) { return g.err.c_str(); }
+extern "C" const char *pcb200_kernel_name(void) { return g.kname; }
 extern "C" int pcb200_abi_version(void) { return PCB200_ABI_VERSION; }
 
 extern "C" int pcb200_init(int local_rank)
@@ -493,6 +495,7 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_time_on) { e0 = next_event(); e1 = next_event(); cudaEventRecord(e0, g.st); }
   if (g.use_global) {
+    g.kname = "rhs_global";
     dim3 blk(32, 4, 2), grd((P.nx + 31) / 32, (P.ny + 3) / 4, (z_hi - z_lo + 1) / 2);
     *nblocks_out = grd.x * grd.y * grd.z;
     if (M && E) rhs_global<true, true, AUXM><<<grd, blk, 0, g.st>>>(a);
@@ -505,7 +508,9 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     *nblocks_out = grd.x * grd.y * grd.z;
     const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
     const bool rw = a.alpha != 0.0;
+    g.kname = "rhs_tma";
     if (g.use_dly && P.lbidiagonal_derij && AUXM < 2 && !E) {
+      g.kname = "rhs_dly";
       a.zchunk = g.zchunk_dly < (z_hi - z_lo) ? g.zchunk_dly : (z_hi - z_lo);
       grd.z = (z_hi - z_lo + a.zchunk - 1) / a.zchunk;
       *nblocks_out = grd.x * grd.y * grd.z;
@@ -527,6 +532,7 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
 #undef LT
     }
   } else {
+    g.kname = "rhs_march";
     a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
     dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
     *nblocks_out = grd.x * grd.y * grd.z;

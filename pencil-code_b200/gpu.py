@@ -131,6 +131,10 @@ class GPU:
     def launch_count(self):
         return int(self.lib.pcb200_launch_count())
 
+    def kernel_name(self):
+        """fused RHS+RK kernel of the last substep launch (rhs_dly / rhs_tma / rhs_march / rhs_global)"""
+        return self.lib.pcb200_kernel_name().decode()
+
     def enable_kernel_timing(self, on=True):
         self._ck(self.lib.pcb200_enable_kernel_timing(int(on)))
 
