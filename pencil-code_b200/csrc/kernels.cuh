@@ -800,3 +800,135 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
     block_reduce_store<AUXM>(red, tid, NTHR, redsm, a.partials, bl);
   }
 }
+
+// ------------------------------------------------------------------------
+// cfl_prepass: dt1_max of the state at the beginning of a time step (isothermal runs).
+// The reference reduces dt1_max over the RHS evaluation of substep 1 and only then updates f
+// (timestep.f90:141-163), which costs a separate axpy pass over f and w.  Without entropy the
+// CFL terms (equ.f90:1086-1151) need only |u|, cs2, rho1 and B = curl A (hydro.f90:3810,
+// noentropy.f90:367, magnetic.f90:5438, viscosity/resistivity constants), so a light z-marching
+// kernel computes them first (56 B/cell read, 6 derivatives) and substep 1 applies the update
+// itself.  Same per-cell formula as hydro_pre/hydro_finish (AUX part); partials[block][RD_DT1].
+// ------------------------------------------------------------------------
+struct CflAcc {
+  const double *sm;     // [3 A fields][2 slots][PE]
+  int cb;               // element offset of this thread's cell in the centre slot
+  double wx[7], wy[7];  // own column of Ax, Ay, planes z-3..z+3
+  template <int R, int K> PC_DEV double x() const { return sm[(R - R_AX) * 2 * PE + cb + K]; }
+  template <int R, int K> PC_DEV double y() const { return sm[(R - R_AX) * 2 * PE + cb + K * HX]; }
+  template <int R, int K> PC_DEV double z() const { return R == R_AX ? wx[3 + K] : wy[3 + K]; }
+};
+
+__device__ __forceinline__ void cp_async16(double *smem_dst, const double *gsrc)
+{
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc));
+}
+
+template <bool MAG>
+__global__ void __launch_bounds__(NTHR, 3) cfl_prepass(const double *__restrict__ f, double *__restrict__ partials, int z_lo, int z_hi, int zchunk)
+{
+  const DevPar &c = c_par;
+  __shared__ __align__(16) double sm[MAG ? 3 * 2 * PE : 2];
+  __shared__ double redsm[8 * NRED];
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx;
+  const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
+  const int zb = z_lo + blockIdx.z * zchunk;
+  const int ze = min(zb + zchunk, z_hi);
+  const bool active = (x0 + tx < c.nx) && (y0 + ty < c.ny);
+  const int lx = min(x0 + tx, c.nx - 1), ly = min(y0 + ty, c.ny - 1);
+  const long long col = (long long)(ly + NG) * c.sy + (lx + NG);
+  // this thread's share of a halo tile: pairs of doubles (16-byte copies) when every row start is
+  // 16-byte aligned (mx even; x0 and HX are even), single doubles otherwise
+  const bool pairs = (c.mx & 1) == 0;
+  const int per = pairs ? 2 : 1;
+  int eoff[3]; long long goff[3]; bool eok[3];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int e = (tid + i * NTHR) * per;
+    const int hy = e / HX, hx = e - hy * HX;
+    eoff[i] = e;
+    eok[i] = e < PE && (x0 + hx + per - 1) < c.mx && (y0 + hy) < c.my;
+    goff[i] = (long long)(y0 + hy) * c.sy + (x0 + hx);
+  }
+  auto stage = [&](int n) {       // centre-plane tiles of interior plane n into slot n&1
+    if (MAG) {
+      const long long pz = (long long)(n + NG) * c.sz;
+#pragma unroll
+      for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+          if (!eok[i]) continue;
+          double *dst = sm + (r * 2 + (n & 1)) * PE + eoff[i];
+          const double *src = f + c.foff[R_AX + r] + pz + goff[i];
+          if (pairs) cp_async16(dst, src); else cp_async8(dst, src);
+        }
+    }
+    cp_async_commit();
+  };
+  CflAcc acc;
+  acc.sm = sm;
+  const double *pu = f + col;
+  if (MAG) {
+#pragma unroll
+    for (int k = 0; k < 7; k++) {
+      acc.wx[k] = __ldg(pu + c.foff[R_AX] + (long long)(zb + k) * c.sz);
+      acc.wy[k] = __ldg(pu + c.foff[R_AY] + (long long)(zb + k) * c.sz);
+    }
+  }
+  stage(zb);
+  double dt1max = 0.0;
+  const double dt1_diffus = (MAG ? fmax(c.nu * c.dxyz_2, c.eta * c.dxyz_2) : c.nu * c.dxyz_2) / c.cdtv;
+  const double advec_cs2 = c.cs20 * c.dxyz_2;
+  // own-cell values are loaded one plane ahead
+  long long idx = (long long)(zb + NG) * c.sz;
+  double ux = __ldg(pu + c.foff[R_UX] + idx), uy = __ldg(pu + c.foff[R_UY] + idx), uz = __ldg(pu + c.foff[R_UZ] + idx);
+  double lnrho = MAG ? __ldg(pu + c.foff[R_LNRHO] + idx) : 0.0;
+  cp_async_wait_all();
+  __syncthreads();
+#pragma unroll 1
+  for (int n = zb; n < ze; n++) {
+    const bool more = n + 1 < ze;
+    double nux = 0.0, nuy = 0.0, nuz = 0.0, nln = 0.0, nwx = 0.0, nwy = 0.0;
+    if (more) {
+      stage(n + 1);
+      idx += c.sz;
+      nux = __ldg(pu + c.foff[R_UX] + idx); nuy = __ldg(pu + c.foff[R_UY] + idx); nuz = __ldg(pu + c.foff[R_UZ] + idx);
+      if (MAG) {
+        nln = __ldg(pu + c.foff[R_LNRHO] + idx);
+        nwx = __ldg(pu + c.foff[R_AX] + idx + 3 * c.sz); nwy = __ldg(pu + c.foff[R_AY] + idx + 3 * c.sz);
+      }
+    }
+    const double advec_uu = fabs(ux) * c.dx_1 + fabs(uy) * c.dy_1 + fabs(uz) * c.dz_1;     // hydro.f90:3810
+    double advec_va2 = 0.0;
+    if (MAG) {
+      acc.cb = (n & 1) * PE + (ty + NG) * HX + tx + NG;
+      const double axy = ddy<R_AX>(acc, c.fy1), axz = ddz<R_AX>(acc, c.fz1);
+      const double ayx = ddx<R_AY>(acc, c.fx1), ayz = ddz<R_AY>(acc, c.fz1);
+      const double azx = ddx<R_AZ>(acc, c.fx1), azy = ddy<R_AZ>(acc, c.fy1);
+      const double bx = azy - ayz, by = axz - azx, bz = ayx - axy;
+      const double rho1 = exp(-lnrho);
+      const double t0 = bx * c.dx_1, t1 = by * c.dy_1, t2 = bz * c.dz_1;
+      advec_va2 = (t0 * t0 + t1 * t1 + t2 * t2) * c.mu01 * rho1;                            // magnetic.f90:5438
+    }
+    const double maxadvec = advec_uu + sqrt(advec_va2 + advec_cs2);
+    const double dt1_advec = maxadvec / c.cdt;
+    const double dt1 = sqrt(dt1_advec * dt1_advec + dt1_diffus * dt1_diffus);             // equ.f90:1149
+    if (active) dt1max = fmax(dt1max, dt1);
+    if (!more) break;
+    cp_async_wait_all();
+    __syncthreads();
+    ux = nux; uy = nuy; uz = nuz; lnrho = nln;
+    if (MAG) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) { acc.wx[k] = acc.wx[k + 1]; acc.wy[k] = acc.wy[k + 1]; }
+      acc.wx[6] = nwx; acc.wy[6] = nwy;
+    }
+  }
+  double red[NRED];
+#pragma unroll
+  for (int q = 0; q < NRED; q++) red[q] = 0.0;
+  red[RD_DT1] = dt1max;
+  const int bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  block_reduce_store<1>(red, tid, NTHR, redsm, partials, bl);
+}

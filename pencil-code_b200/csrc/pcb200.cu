@@ -67,6 +67,7 @@ struct Ctx {
   bool use_dly = true;          // rhs_dly (delayed z-mixed terms, tensor-memory history); PCB200_KERNEL=tma selects rhs_tma
   int zchunk = 0;
   const char *kname = "";        // kernel of the last substep launch
+  bool use_prepass = true;      // isothermal runs: CFL pre-pass + fused update in substep 1 (PCB200_PREPASS=0: axpy pass)
   int zchunk_dly = 0;           // rhs_dly pays 6 extra steps per chunk: fewer, longer chunks
   int64_t launches = 0;
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
@@ -132,6 +133,8 @@ extern "C" int pcb200_init(int local_rank)
     g.use_global = k && !strcmp(k, "global");
     g.use_cpasync = k && !strcmp(k, "cpasync");
     g.use_dly = !k || !strcmp(k, "dly");
+    const char *pp = getenv("PCB200_PREPASS");
+    g.use_prepass = !pp || atoi(pp) != 0;
     const char *t = getenv("PCB200_TIME_RHS");
     g.time_rhs = t && atoi(t) != 0;
     g.inited = true;
@@ -274,7 +277,8 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
     const int zcmin = g.zchunk < g.zchunk_dly ? g.zchunk : g.zchunk_dly;
     const size_t nb_m = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + zcmin - 1) / zcmin + 2);
     const size_t nb_g = (size_t)((P.nx + 31) / 32) * ((P.ny + 3) / 4) * ((P.nz + 1) / 2 + 2);
-    const size_t need = (nb_m > nb_g ? nb_m : nb_g) * NRED;
+    const size_t nb_p = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + 63) / 64);   // cfl_prepass
+    const size_t need = std::max(std::max(nb_m, nb_g), nb_p) * NRED;
     if (need > g.npartials) { if (g.partials) cudaFree(g.partials); CK(cudaMalloc(&g.partials, need * sizeof(double))); g.npartials = need; }
   }
   CK(cudaMemcpyToSymbolAsync(c_par, &h, sizeof(DevPar), 0, cudaMemcpyHostToDevice, g.st));
@@ -935,7 +939,28 @@ static int do_substep(int isub, int ldiagnos)
     if ((rc = part_pencils(fin, need_dt))) return rc;
   }
   int nb0 = 0, nb1 = 0, nb2 = 0;
-  if (!multi) {
+  // Isothermal runs: dt from a light CFL pre-pass over the start-of-step state, so that substep 1
+  // applies the 2N update itself and the separate axpy pass over f and w disappears.
+  const bool prepass = need_dt && !ldiagnos && !P.lentropy && g.use_prepass;
+  if (prepass) {
+    if (multi) CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0));
+    const int zc = 64;
+    dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (P.nz + zc - 1) / zc);
+    if (P.lmagnetic) cfl_prepass<true><<<grd, blk, 0, g.st>>>(fin, g.partials, 0, P.nz, zc);
+    else cfl_prepass<false><<<grd, blk, 0, g.st>>>(fin, g.partials, 0, P.nz, zc);
+    reduce_partials<<<1, NRED * 32, 0, g.st>>>(g.partials, (int)(grd.x * grd.y * grd.z), g.red_dev);
+    const double floor1 = P.dtmax != 0.0 ? 1.0 / P.dtmax : 0.0;
+    finish_dt<<<1, 32, 0, g.st>>>(g.red_dev, floor1, g.dt_dev, g.part.on ? g.part.dt1 : nullptr);
+    g.launches += 3;
+    if (g.nranks > 1) {
+      NK(g.nccl.AllReduce(g.dt_dev + 1, g.dt_dev + 1, 1, 8, 2 /*ncclMax*/, g.comm, g.st));     // set_dt, sub.f90:3909
+      set_dt_from_dt1<<<1, 32, 0, g.st>>>(g.dt_dev);
+      g.launches++;
+    }
+    CK(cudaGetLastError());
+    a.write_f = 1;
+    if ((rc = launch_rhs(0, a, 0, P.nz, 0, &nb0))) return rc;
+  } else if (!multi) {
     if ((rc = launch_rhs(auxm, a, 0, P.nz, 0, &nb0))) return rc;
   } else {
     // interior planes overlap with the halo exchange (general.f90:267-279 / gpu_astaroth.cc:162-166)
@@ -964,12 +989,12 @@ static int do_substep(int isub, int ldiagnos)
     }
     CK(cudaGetLastError());
   }
-  if (auxm > 0) {
+  if (auxm > 0 && !prepass) {
     reduce_partials<<<1, NRED * 32, 0, g.st>>>(g.partials, nb0 + nb1 + nb2, g.red_dev);
     g.launches++;
     CK(cudaGetLastError());
   }
-  if (need_dt) {
+  if (need_dt && !prepass) {
     const double floor1 = P.dtmax != 0.0 ? 1.0 / P.dtmax : 0.0;
     finish_dt<<<1, 32, 0, g.st>>>(g.red_dev, floor1, g.dt_dev, g.part.on ? g.part.dt1 : nullptr);
     g.launches++;
