@@ -51,6 +51,9 @@ struct Ctx {
   size_t nelem = 0;             // mw*mvar
   double *f[2] = {nullptr, nullptr}, *w = nullptr;
   CUtensorMap tmap[2];          // TMA view of f[0], f[1] as (mx, my, mz*mvar)
+  CUtensorMap tmap4[2];         // rhs_dly: f[0], f[1] as (mx, my, mz, mvar), box {HX,HY,1,mvar}
+  CUtensorMap tmap_wu, tmap_wr; // rhs_dly: w as (mx, my, mz, mvar), boxes {TX+2,TY,1,3} and {TX+2,TY,1,mvar-3} at x0+2 (16-byte aligned start)
+  bool have_dly = false;        // standard variable order + 4-D maps encoded
   bool have_tma = false;
   int cur = 0;
   double *partials = nullptr; size_t npartials = 0;
@@ -155,6 +158,7 @@ static void free_fields()
 static int make_tensor_maps()
 {
   g.have_tma = false;
+  g.have_dly = false;
   const DevPar &h = g.hp;
   if ((h.mx * 8) % 16 != 0) return PCB200_OK;          // global strides must be multiples of 16 B: cp.async path instead
   typedef CUresult (*encode_t)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -176,6 +180,31 @@ static int make_tensor_maps()
     if (r != CUDA_SUCCESS) return fail(PCB200_ECUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   }
   g.have_tma = true;
+  // rhs_dly: one 4-D box per plane, which needs the reference's standard registration order
+  // (register.f90:124-135) and no further variables
+  g.have_dly = false;
+  const pcb200_params &P = g.P;
+  const int nf = 4 + (P.lmagnetic ? 3 : 0) + (P.lentropy ? 1 : 0);
+  bool std_order = P.iux == 1 && P.iuy == 2 && P.iuz == 3 && P.ilnrho == 4 && P.mvar == nf;
+  if (P.lentropy) std_order = std_order && P.iss == 5;
+  if (P.lmagnetic) { const int a0 = P.lentropy ? 6 : 5; std_order = std_order && P.iax == a0 && P.iay == a0 + 1 && P.iaz == a0 + 2; }
+  if (!std_order) return PCB200_OK;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)h.mx, (cuuint64_t)h.my, (cuuint64_t)h.mz, (cuuint64_t)h.mvar};
+    cuuint64_t strides[3] = {(cuuint64_t)h.mx * 8, (cuuint64_t)h.sz * 8, (cuuint64_t)h.mw * 8};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    for (int i = 0; i < 4; i++) {
+      cuuint32_t box[4] = {HX, HY, 1, (cuuint32_t)h.mvar};
+      CUtensorMap *tm = i < 2 ? &g.tmap4[i] : (i == 2 ? &g.tmap_wu : &g.tmap_wr);
+      void *base = i < 2 ? (void *)g.f[i] : (void *)g.w;
+      if (i >= 2) { box[0] = TX + 2; box[1] = TY; box[3] = i == 2 ? 3 : (cuuint32_t)(h.mvar - 3); }
+      CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, base, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) return fail(PCB200_ECUDA, "cuTensorMapEncodeTiled (4-D) failed (" + std::to_string((int)r) + ")");
+    }
+  }
+  g.have_dly = true;
   return PCB200_OK;
 }
 
@@ -513,17 +542,18 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
     const bool rw = a.alpha != 0.0;
     g.kname = "rhs_tma";
-    if (g.use_dly && P.lbidiagonal_derij && AUXM < 2 && !E) {
+    if (g.use_dly && g.have_dly && P.lbidiagonal_derij && AUXM < 2 && !E) {
+      const CUtensorMap &tm4 = g.tmap4[a.f_in == g.f[0] ? 0 : 1];
       g.kname = "rhs_dly";
       a.zchunk = g.zchunk_dly < (z_hi - z_lo) ? g.zchunk_dly : (z_hi - z_lo);
       grd.z = (z_hi - z_lo + a.zchunk - 1) / a.zchunk;
       *nblocks_out = grd.x * grd.y * grd.z;
       // centre-plane-only stencils, z-mixed terms finished three planes late from tensor memory
       constexpr int AX = AUXM < 2 ? AUXM : 0;
-      if (M) { if (rw) rhs_dly<true, false, 0, true><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm);
-               else    rhs_dly<true, false, AX, false><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm); }
-      else   { if (rw) rhs_dly<false, false, 0, true><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm);
-               else    rhs_dly<false, false, AX, false><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm); }
+      if (M) { if (rw) rhs_dly<true, false, 0, true><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
+               else    rhs_dly<true, false, AX, false><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
+      else   { if (rw) rhs_dly<false, false, 0, true><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
+               else    rhs_dly<false, false, AX, false><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
     } else {
     // the old 2N register is only read on substeps 2,3, which never need the reductions
 #define LT(M, E) do { if (P.lbidiagonal_derij) { \
@@ -548,6 +578,12 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
   if (g_time_on) cudaEventRecord(e1, g.st);
   g.launches++;
   CK(cudaGetLastError());
+  if (getenv("PCB200_DEBUG_SYNC")) {      // debugging aid: attribute a device fault to the launch that caused it
+    cudaError_t es = cudaStreamSynchronize(g.st);
+    if (es != cudaSuccess)
+      return fail(PCB200_ECUDA, std::string(g.kname) + " auxm=" + std::to_string(AUXM) + " rw=" + std::to_string(a.alpha != 0.0) + " z=[" +
+                  std::to_string(z_lo) + "," + std::to_string(z_hi) + ") zchunk=" + std::to_string(a.zchunk) + ": " + cudaGetErrorString(es));
+  }
   return PCB200_OK;
 }
 static int launch_rhs(int auxm, const SubstepArgs &a, int z_lo, int z_hi, size_t part_off, int *nb)

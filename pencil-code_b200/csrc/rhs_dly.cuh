@@ -61,16 +61,28 @@ template <int NC> PC_DEV void tm_ld_group(unsigned t0, int g, unsigned *r)   // 
 }
 PC_DEV double tm_dbl(const unsigned *r, int i) { return __hiloint2double((int)r[2 * i + 1], (int)r[2 * i]); }
 
-// ring position of a role (absent roles are compacted away)
+// Position of a role inside a ring slot = its storage slot in f for the standard registration
+// order of the reference (register.f90:124-135: ux,uy,uz,lnrho,[ss],ax,ay,az), so that ONE 4-D TMA
+// box {HX,HY,1,mvar} brings a whole plane.  The host checks the order and mvar before it selects
+// this kernel (other layouts run rhs_tma).
 template <bool MAG, bool ENT> PC_DEV constexpr int dly_fidx(int R)
-{ return R < 3 ? R : (R < 6 ? R : (R == R_LNRHO ? (MAG ? 6 : 3) : (MAG ? 7 : 4))); }
+{ return R < 3 ? R : (R == R_LNRHO ? 3 : (R == R_SS ? 4 : (R - R_AX) + (ENT ? 5 : 4))); }
+__device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *tm, int x, int y, int z, int v, unsigned long long *bar)
+{
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+               ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(z), "r"(v), "r"(smem_u32(bar)) : "memory");
+}
 
 template <bool MAG, bool ENT> struct DlyCfg {
   static constexpr int NF = 4 + (MAG ? 3 : 0) + (ENT ? 1 : 0);
   static constexpr int NC = MAG ? 6 : 3;                      // z-mixed combinations kept per plane and distance k
-  static constexpr int NDBL = NF * NSD * PEP;
-  static constexpr int NWB = 2 * NF * NTHR;                   // old-2N-register staging: [2 steps][field][thread]
-  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + NWB + 8 * NRED + 6) + 128;
+  static constexpr int SLD = (NF * PE + 15) / 16 * 16;        // doubles per ring slot [field][HY][HX], padded to 128 B
+  static constexpr int NDBL = NSD * SLD;
+  // old-2N-register staging [2 steps][field][TY][WTX]: a TMA box must start at a 16-byte aligned
+  // global address (measured: x0+3 faults, tools/tma4d_test.cu), so the tile starts at x0+2
+  static constexpr int WTX = TX + 2, WTE = WTX * TY;
+  static constexpr int NWB = 2 * NF * WTE;
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + NWB + 8 * NRED + 8) + 128;
   // tensor-memory groups per thread (NC doubles each), see DLY_NGRP
   static_assert(DLY_NGRP * NC * 2 <= 256, "tensor-memory budget per thread");
 };
@@ -83,7 +95,7 @@ struct DlyAcc {
   const double *smem0;
   unsigned cb;            // byte offset of this thread's cell in the ring slot of the centre plane
   double w[NROLE][7];     // own column, planes z-3..z+3
-  template <int R, int OFF> PC_DEV double cenv() const { return lds_at(smem0, cb, dly_fidx<MAG, ENT>(R) * NSD * PEP + OFF); }
+  template <int R, int OFF> PC_DEV double cenv() const { return lds_at(smem0, cb, dly_fidx<MAG, ENT>(R) * PE + OFF); }
   template <int R> PC_DEV double c() const { return w[R][3]; }
   template <int R, int K> PC_DEV double x() const { return cenv<R, K>(); }
   template <int R, int K> PC_DEV double y() const { return cenv<R, K * HX>(); }
@@ -114,8 +126,11 @@ PC_DEV void dly_combos(const DlyAcc<MAG, ENT> &a, const DevPar &c, double *__res
 }
 
 template <bool MAG, bool ENT, int AUXM, bool RW>
-__global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_constant__ CUtensorMap tmap)
+__global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_constant__ CUtensorMap tmap,
+                                                   const __grid_constant__ CUtensorMap tmap_wu, const __grid_constant__ CUtensorMap tmap_wr)
 {
+  // tmap: f_in as (mx,my,mz,mvar), box {HX,HY,1,mvar}.  tmap_wu / tmap_wr: the 2N register w, boxes
+  // {TX+2,TY,1,3} (u) and {TX+2,TY,1,mvar-3} (the other fields) -- own cells only.
   static_assert(AUXM < 2, "full diagnostics run through rhs_tma");
   typedef DlyCfg<MAG, ENT> Cfg;
   constexpr int NC = Cfg::NC, NF = Cfg::NF;
@@ -126,8 +141,8 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   double *wbuf = smem + (size_t)Cfg::NDBL;
   double *redsm = wbuf + Cfg::NWB;
   unsigned long long *bar = reinterpret_cast<unsigned long long *>(redsm + 8 * NRED);
-  unsigned *tbase_sm = reinterpret_cast<unsigned *>(bar + 4);
-  constexpr unsigned BOX_BYTES = PE * 8;
+  unsigned *tbase_sm = reinterpret_cast<unsigned *>(bar + 6);
+  constexpr unsigned BOX_BYTES = NF * PE * 8;       // one plane of every field
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx, warp = tid >> 5;
   const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
@@ -145,12 +160,15 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   // full[0]); two barriers because plane q+1 is armed while plane q may still be in flight.
   // empty[s&1]: phase s/2 completes when all NTHR threads are done with step s (warps drift up to
   // two steps apart, so consecutive steps must not share a barrier).
-  unsigned long long *full = bar, *empty = bar + 2;
+  // wfull[s&1]: phase s/2 = the w tiles of step s have landed (issued one step ahead).
+  unsigned long long *full = bar, *empty = bar + 2, *wfull = bar + 4;
   if (tid == 0) {
     mbar_init(full, 1);
     mbar_init(full + 1, 1);
     mbar_init(empty, NTHR);
     mbar_init(empty + 1, NTHR);
+    mbar_init(wfull, 1);
+    mbar_init(wfull + 1, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -164,17 +182,22 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   const unsigned t0 = *tbase_sm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * 256);
 
   auto issue_plane = [&](int q, int sl) __attribute__((always_inline)) {     // ring plane q (padded z = zb+q) of every field into slot sl = q % NSD
-    unsigned long long *fb = full + (q >= 4 ? (q & 1) : 0);
-#pragma unroll
-    for (int r = 0; r < NROLE; r++) {
-      if (!role_present<MAG, ENT>(r)) continue;
-      tma_load_3d(ring + ((size_t)dly_fidx<MAG, ENT>(r) * NSD + sl) * PEP, &tmap, x0, y0, c.slot[r] * c.mz + zb + q, fb);
-    }
+    tma_load_4d(ring + (size_t)sl * Cfg::SLD, &tmap, x0, y0, zb + q, 0, full + (q >= 4 ? (q & 1) : 0));
+  };
+  // The old 2N register w of step s is fetched by TMA one step ahead into wbuf[s&1][field][TY][TX]
+  // (own cells only; no per-thread loads, no registers held across the stencils).  u belongs to plane n-3.
+  auto issue_w = [&](int s) __attribute__((always_inline)) {
+    if (!RW) return;
+    double *dst = wbuf + (size_t)(s & 1) * NF * Cfg::WTE;
+    mbar_expect_tx(wfull + (s & 1), (unsigned)(NF * Cfg::WTE * 8));
+    tma_load_4d(dst, &tmap_wu, x0 + NG - 1, y0 + NG, zb + s - (s >= 6 ? 3 : 0), 0, wfull + (s & 1));
+    tma_load_4d(dst + 3 * Cfg::WTE, &tmap_wr, x0 + NG - 1, y0 + NG, zb + s, 3, wfull + (s & 1));
   };
   if (tid == 0) {
-    mbar_expect_tx(full, (unsigned)(NF * 5 * BOX_BYTES));
+    mbar_expect_tx(full, (unsigned)(5 * BOX_BYTES));
 #pragma unroll 1
     for (int q = 0; q < 5; q++) issue_plane(q, q);
+    issue_w(0);
   }
   // zero the history and the pending slots (defined values in the first steps)
   {
@@ -198,25 +221,9 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   for (int r = 0; r < NROLE; r++) {
     if (!role_present<MAG, ENT>(r)) continue;
 #pragma unroll
-    for (int k = 0; k < 4; k++) acc.w[r][3 + k] = ring[((size_t)dly_fidx<MAG, ENT>(r) * NSD + k) * PEP + tb];
+    for (int k = 0; k < 4; k++) acc.w[r][3 + k] = ring[(size_t)k * Cfg::SLD + dly_fidx<MAG, ENT>(r) * PE + tb];
   }
 
-  // The old 2N register w of step s is staged by cp.async one step ahead into wbuf[s&1][field][tid]
-  // (own cell only: no barrier, no registers held across the stencils).  u belongs to plane n-3.
-  auto stage_w = [&](const int s) __attribute__((always_inline)) {
-    if (RW && s < nstep) {
-      const long long idx = (long long)(zb + s) * c.sz + col;
-      const long long idu = s >= 6 ? idx - 3 * c.sz : idx;
-      double *dst = wbuf + (size_t)(s & 1) * NF * NTHR + tid;
-#pragma unroll
-      for (int r = 0; r < NROLE; r++) {
-        if (!role_present<MAG, ENT>(r)) continue;
-        cp_async8(dst + dly_fidx<MAG, ENT>(r) * NTHR, a.w + (r < 3 ? idu : idx) + c.foff[r]);
-      }
-    }
-    if (RW) cp_async_commit();
-  };
-  stage_w(0);
   int c5 = 0, c6 = 0, c7 = 0, c3 = 0;         // s % 5, s % 6, s % 7, s % 3
   // one step; FULL: centre plane and plane n-3 both inside the chunk (no masks)
   auto step = [&](const int s, auto full_tag) __attribute__((always_inline)) {
@@ -226,15 +233,20 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     bool issued = true;
     if (more && tid == 0) {
       issued = s == 0 || mbar_test_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
-      if (issued) { mbar_expect_tx(full + ((s + 1) & 1), (unsigned)(NF * BOX_BYTES)); issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1); }
+      if (issued) { mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES); issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1); }
+    }
+    // the w tiles of step s+1 reuse the buffer of step s-1: same condition as the plane of step s-1
+    bool w_issued = true;
+    if (RW && s + 1 < nstep && tid == 0) {
+      w_issued = issued && (more || s == 0 || mbar_test_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1)));
+      if (w_issued) issue_w(s + 1);
     }
     const bool doA = FULL || (s >= 3 && s < nzc + 3);   // phase A produces output (centre plane inside the chunk)
     const bool doB = FULL || s >= 6;                    // phase B finishes plane n-3
     const long long idx = (long long)(n + NG) * c.sz + col;
     const long long idxB = idx - 3 * c.sz;
-    stage_w(s + 1);
     // ---- phase A: everything of plane n except the z-mixed terms ----
-    acc.cb = (unsigned)((c6 * PEP + tb) * 8);
+    acc.cb = (unsigned)((c6 * Cfg::SLD + tb) * 8);
     // the pre-scaled x/y differences go to the history at once (slots that are not read in this step)
     {
       double d[6];
@@ -258,8 +270,12 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     hydro_finish<MAG, ENT, (AUXM > 0)>(c, hp, m, rhs, aux);
     if (tid == 0 && !issued) {
       mbar_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
-      mbar_expect_tx(full + ((s + 1) & 1), (unsigned)(NF * BOX_BYTES));
+      mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES);
       issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1);
+    }
+    if (RW && tid == 0 && !w_issued) {
+      mbar_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
+      issue_w(s + 1);
     }
     // ---- phase B: finish du/dt of plane n-3 ----
     unsigned h3[2 * NC], h2a[2 * NC], h2b[2 * NC], h1a[2 * NC], h1b[2 * NC], pn[2 * NC];
@@ -273,12 +289,12 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     tm_ld_group<NC>(t0, pg, pn);
     double wold[NROLE];
     if (RW) {
-      asm volatile("cp.async.wait_group 1;" ::: "memory");          // this step's group has landed (next step's may be in flight)
-      const double *src = wbuf + (size_t)(s & 1) * NF * NTHR + tid;
+      mbar_wait(wfull + (s & 1), (unsigned)((s >> 1) & 1));         // this step's w tiles have landed
+      const double *src = wbuf + (size_t)(s & 1) * NF * Cfg::WTE + ty * Cfg::WTX + tx + 1;
 #pragma unroll
       for (int r = 0; r < NROLE; r++) {
         if (!role_present<MAG, ENT>(r)) continue;
-        wold[r] = src[dly_fidx<MAG, ENT>(r) * NTHR];
+        wold[r] = src[dly_fidx<MAG, ENT>(r) * Cfg::WTE];
       }
     }
     // fields without z-mixed terms leave while the tensor-memory loads are in flight
@@ -328,7 +344,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
       if (!role_present<MAG, ENT>(r)) continue;
 #pragma unroll
       for (int k = 0; k < 6; k++) asm volatile("mov.b64 %0, %1;" : "=d"(acc.w[r][k]) : "d"(acc.w[r][k + 1]));   // one move each, in this order
-      acc.w[r][6] = have4 ? ring[((size_t)dly_fidx<MAG, ENT>(r) * NSD + nl) * PEP + tb] : 0.0;
+      acc.w[r][6] = have4 ? ring[(size_t)nl * Cfg::SLD + dly_fidx<MAG, ENT>(r) * PE + tb] : 0.0;
     }
     mbar_arrive(empty + (s & 1));
     c5 = c5 == 4 ? 0 : c5 + 1;
