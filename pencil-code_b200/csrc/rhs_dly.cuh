@@ -78,11 +78,11 @@ template <bool MAG, bool ENT> struct DlyCfg {
   static constexpr int NC = MAG ? 6 : 3;                      // z-mixed combinations kept per plane and distance k
   static constexpr int SLD = (NF * PE + 15) / 16 * 16;        // doubles per ring slot [field][HY][HX], padded to 128 B
   static constexpr int NDBL = NSD * SLD;
-  // old-2N-register staging [2 steps][field][TY][WTX]: a TMA box must start at a 16-byte aligned
+  // old-2N-register staging [3 steps][field][TY][WTX]: a TMA box must start at a 16-byte aligned
   // global address (measured: x0+3 faults, tools/tma4d_test.cu), so the tile starts at x0+2
   static constexpr int WTX = TX + 2, WTE = WTX * TY;
-  static constexpr int NWB = 2 * NF * WTE;
-  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + NWB + 8 * NRED + 8) + 128;
+  static constexpr int NWB = 3 * NF * WTE;
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)NDBL + NWB + 8 * NRED + 10) + 128;
   // tensor-memory groups per thread (NC doubles each), see DLY_NGRP
   static_assert(DLY_NGRP * NC * 2 <= 256, "tensor-memory budget per thread");
 };
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   double *wbuf = smem + (size_t)Cfg::NDBL;
   double *redsm = wbuf + Cfg::NWB;
   unsigned long long *bar = reinterpret_cast<unsigned long long *>(redsm + 8 * NRED);
-  unsigned *tbase_sm = reinterpret_cast<unsigned *>(bar + 6);
+  unsigned *tbase_sm = reinterpret_cast<unsigned *>(bar + 7);
   constexpr unsigned BOX_BYTES = NF * PE * 8;       // one plane of every field
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx, warp = tid >> 5;
@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   // full[0]); two barriers because plane q+1 is armed while plane q may still be in flight.
   // empty[s&1]: phase s/2 completes when all NTHR threads are done with step s (warps drift up to
   // two steps apart, so consecutive steps must not share a barrier).
-  // wfull[s&1]: phase s/2 = the w tiles of step s have landed (issued one step ahead).
+  // wfull[s%3]: phase s/3 = the w tiles of step s have landed (issued two steps ahead).
   unsigned long long *full = bar, *empty = bar + 2, *wfull = bar + 4;
   if (tid == 0) {
     mbar_init(full, 1);
@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     mbar_init(empty + 1, NTHR);
     mbar_init(wfull, 1);
     mbar_init(wfull + 1, 1);
+    mbar_init(wfull + 2, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -184,20 +185,21 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   auto issue_plane = [&](int q, int sl) __attribute__((always_inline)) {     // ring plane q (padded z = zb+q) of every field into slot sl = q % NSD
     tma_load_4d(ring + (size_t)sl * Cfg::SLD, &tmap, x0, y0, zb + q, 0, full + (q >= 4 ? (q & 1) : 0));
   };
-  // The old 2N register w of step s is fetched by TMA one step ahead into wbuf[s&1][field][TY][TX]
+  // The old 2N register w of step s is fetched by TMA two steps ahead into wbuf[s%3][field][TY][WTX]
   // (own cells only; no per-thread loads, no registers held across the stencils).  u belongs to plane n-3.
-  auto issue_w = [&](int s) __attribute__((always_inline)) {
+  auto issue_w = [&](int s, int s3) __attribute__((always_inline)) {   // s3 = s % 3
     if (!RW) return;
-    double *dst = wbuf + (size_t)(s & 1) * NF * Cfg::WTE;
-    mbar_expect_tx(wfull + (s & 1), (unsigned)(NF * Cfg::WTE * 8));
-    tma_load_4d(dst, &tmap_wu, x0 + NG - 1, y0 + NG, zb + s - (s >= 6 ? 3 : 0), 0, wfull + (s & 1));
-    tma_load_4d(dst + 3 * Cfg::WTE, &tmap_wr, x0 + NG - 1, y0 + NG, zb + s, 3, wfull + (s & 1));
+    double *dst = wbuf + (size_t)s3 * NF * Cfg::WTE;
+    mbar_expect_tx(wfull + s3, (unsigned)(NF * Cfg::WTE * 8));
+    tma_load_4d(dst, &tmap_wu, x0 + NG - 1, y0 + NG, zb + s - (s >= 6 ? 3 : 0), 0, wfull + s3);
+    tma_load_4d(dst + 3 * Cfg::WTE, &tmap_wr, x0 + NG - 1, y0 + NG, zb + s, 3, wfull + s3);
   };
   if (tid == 0) {
     mbar_expect_tx(full, (unsigned)(5 * BOX_BYTES));
 #pragma unroll 1
     for (int q = 0; q < 5; q++) issue_plane(q, q);
-    issue_w(0);
+    issue_w(0, 0);
+    issue_w(1, 1);
   }
   // zero the history and the pending slots (defined values in the first steps)
   {
@@ -225,21 +227,22 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   }
 
   int c5 = 0, c6 = 0, c7 = 0, c3 = 0;         // s % 5, s % 6, s % 7, s % 3
+  unsigned p3 = 0;                            // (s / 3) & 1
   // one step; FULL: centre plane and plane n-3 both inside the chunk (no masks)
   auto step = [&](const int s, auto full_tag) __attribute__((always_inline)) {
     constexpr bool FULL = decltype(full_tag)::value;
     const int n = zb - NG + s;                // centre plane, interior-relative
     const bool more = s + 5 < nstep;          // ring plane s+5 exists: issue it into the slot of plane s-1
+    const bool morew = RW && s + 2 < nstep;   // w tiles of step s+2 into the buffer of step s-1
+    // both overwrite what step s-1 used: wait for "empty" of step s-1 (probe now, block after the stencils)
+    auto issue_all = [&]() __attribute__((always_inline)) {
+      if (more) { mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES); issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1); }
+      if (morew) issue_w(s + 2, c3 == 0 ? 2 : c3 - 1);
+    };
     bool issued = true;
-    if (more && tid == 0) {
+    if ((more || morew) && tid == 0) {
       issued = s == 0 || mbar_test_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
-      if (issued) { mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES); issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1); }
-    }
-    // the w tiles of step s+1 reuse the buffer of step s-1: same condition as the plane of step s-1
-    bool w_issued = true;
-    if (RW && s + 1 < nstep && tid == 0) {
-      w_issued = issued && (more || s == 0 || mbar_test_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1)));
-      if (w_issued) issue_w(s + 1);
+      if (issued) issue_all();
     }
     const bool doA = FULL || (s >= 3 && s < nzc + 3);   // phase A produces output (centre plane inside the chunk)
     const bool doB = FULL || s >= 6;                    // phase B finishes plane n-3
@@ -270,12 +273,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     hydro_finish<MAG, ENT, (AUXM > 0)>(c, hp, m, rhs, aux);
     if (tid == 0 && !issued) {
       mbar_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
-      mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES);
-      issue_plane(s + 5, c6 == 0 ? NSD - 1 : c6 - 1);
-    }
-    if (RW && tid == 0 && !w_issued) {
-      mbar_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
-      issue_w(s + 1);
+      issue_all();
     }
     // ---- phase B: finish du/dt of plane n-3 ----
     unsigned h3[2 * NC], h2a[2 * NC], h2b[2 * NC], h1a[2 * NC], h1b[2 * NC], pn[2 * NC];
@@ -289,8 +287,8 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     tm_ld_group<NC>(t0, pg, pn);
     double wold[NROLE];
     if (RW) {
-      mbar_wait(wfull + (s & 1), (unsigned)((s >> 1) & 1));         // this step's w tiles have landed
-      const double *src = wbuf + (size_t)(s & 1) * NF * Cfg::WTE + ty * Cfg::WTX + tx + 1;
+      mbar_wait(wfull + c3, p3);                                    // this step's w tiles have landed
+      const double *src = wbuf + (size_t)c3 * NF * Cfg::WTE + ty * Cfg::WTX + tx + 1;
 #pragma unroll
       for (int r = 0; r < NROLE; r++) {
         if (!role_present<MAG, ENT>(r)) continue;
@@ -350,7 +348,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     c5 = c5 == 4 ? 0 : c5 + 1;
     c6 = c6 == 5 ? 0 : c6 + 1;
     c7 = c7 == 6 ? 0 : c7 + 1;
-    c3 = c3 == 2 ? 0 : c3 + 1;
+    if (c3 == 2) { c3 = 0; p3 ^= 1u; } else c3++;
   };
   {
     int s = 0;
