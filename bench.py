@@ -269,9 +269,10 @@ def main():
                      "traffic": traffic, "peak_source": peak_src, "kernel": "%s<MAG=1,ENT=%d>" % (dev.kernel_name(), int(args.entropy)), "launches_timed": kcount,
                      "avg_launch_ms": kms, "kernel_ms_per_substep": ksub, "algorithmic_bytes_per_cell": b_alg,
                      "step_frac": cells_local * b_alg * 3 / (ms / args.steps * 1e-3) / 1e9 / peak,
-                     # with ldt the f write of substep 1 is done by axpy_update, not by this kernel:
-                     # its own share of the SURVEY 8d bytes is 9/10
-                     "frac_kernel_own_bytes": (0.9 * ach / peak) if ach else None},
+                     # where the CFL pre-pass does not apply (entropy, PCB200_PREPASS=0) the f write of substep 1 is
+                     # done by axpy_update, not by this kernel: its own share of the SURVEY 8d bytes is then 9/10
+                     "frac_kernel_own_bytes": ((0.9 if (args.entropy or os.environ.get("PCB200_PREPASS", "1") == "0") else 1.0)
+                                               * ach / peak) if ach else None},
         "clocks": clk, "gpu_launches": launches,
     }
     if e2e:
