@@ -30,5 +30,12 @@ struct DevPar {
   double fx1, fy1, fz1;          // dx_1/60 ...
   double fx2, fy2, fz2;          // dx_1^2 ...
   double fxy, fyz, fzx;          // dx_1*dy_1/720 ...
+  // pre-scaled stencil coefficients (constant-bank operands: one FMA per tap, no separate scaling)
+  double k1x[3], k1y[3], k1z[3]; // f1*{45,-9,1}
+  double k2x[4], k2y[4], k2z[4]; // f2*{-490,270,-27,2}/180
+  double k2yz0, k2zx0, k2xy0;    // centre coefficients of the pair sums d2y+d2z, d2z+d2x, d2x+d2y
+  double k2xyz0;                 // ... and of the full Laplacian
+  double kxy[3], kyz[3], kzx[3]; // fij*{270,-27,2}
+  double dlyu[3][2], dlya[3][2]; // rhs_dly history scales: nu/3*c_k*{fzx,fyz} and mu01*c_k*{fzx,fyz}
   const double *zprof[PCB200_NPROF];   // device pointers, nz values each
 };

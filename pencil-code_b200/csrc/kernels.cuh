@@ -96,6 +96,7 @@ __global__ void reduce_partials(const double *__restrict__ partials, int nblocks
 // accessor over global memory
 // ------------------------------------------------------------------------
 struct GlobalAcc {
+  static constexpr bool PS = true;
   const double *p[NROLE];
   long long sy, sz;
   bool bd;
@@ -183,6 +184,7 @@ PC_DEV double lds_at(const double *base, unsigned byteoff, int imm_elems)
 
 template <bool MAG, bool ENT>
 struct MarchAcc {
+  static constexpr bool PS = true;
   const double *smem0;  // dynamic shared memory: ring [ring role][NSLOT][PE], then plain [plain role][2][PE]
   unsigned sb[7];       // byte offset of this thread's cell in the ring slot of plane z+k, k=-3..3
   unsigned pb;          // byte offset of this thread's cell in the plain-field slot of plane z
@@ -610,6 +612,7 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, in
 
 template <bool MAG, bool ENT, bool BD = true>
 struct TmaAcc {
+  static constexpr bool PS = !(MAG && ENT);     // see physics.cuh: the 8-variable kernel spills more with the pre-scaled form
   PC_DEV constexpr bool bidiag() const { return BD; }
   const double *smem0;  // ring [ring role][NSLOT][PEP], then plain [plain role][2][PEP]
   unsigned sb[7];       // byte offset of this thread's cell in the ring slot of plane z+k, k=-3..3
@@ -789,7 +792,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
     for (int r = 0; r < NROLE; r++) {
       if (!role_present<MAG, ENT>(r)) continue;
 #pragma unroll
-      for (int k = 0; k < 6; k++) asm volatile("mov.b64 %0, %1;" : "=d"(acc.w[r][k]) : "d"(acc.w[r][k + 1]));   // one move each, in this order
+      for (int k = 0; k < 6; k++) acc.w[r][k] = acc.w[r][k + 1];
       if (r < 6) acc.w[r][6] = ring[((size_t)r * NSLOT + ((q0 + 7) & (NSLOT - 1))) * PEP + tb];
       else acc.w[r][6] = wnext[r];
     }
@@ -811,6 +814,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
 // itself.  Same per-cell formula as hydro_pre/hydro_finish (AUX part); partials[block][RD_DT1].
 // ------------------------------------------------------------------------
 struct CflAcc {
+  static constexpr bool PS = true;
   const double *sm;     // [3 A fields][2 slots][PE]
   int cb;               // element offset of this thread's cell in the centre slot
   double wx[7], wy[7];  // own column of Ax, Ay, planes z-3..z+3
@@ -903,9 +907,9 @@ __global__ void __launch_bounds__(NTHR, 3) cfl_prepass(const double *__restrict_
     double advec_va2 = 0.0;
     if (MAG) {
       acc.cb = (n & 1) * PE + (ty + NG) * HX + tx + NG;
-      const double axy = ddy<R_AX>(acc, c.fy1), axz = ddz<R_AX>(acc, c.fz1);
-      const double ayx = ddx<R_AY>(acc, c.fx1), ayz = ddz<R_AY>(acc, c.fz1);
-      const double azx = ddx<R_AZ>(acc, c.fx1), azy = ddy<R_AZ>(acc, c.fy1);
+      const double axy = ddy<R_AX>(acc, c), axz = ddz<R_AX>(acc, c);
+      const double ayx = ddx<R_AY>(acc, c), ayz = ddz<R_AY>(acc, c);
+      const double azx = ddx<R_AZ>(acc, c), azy = ddy<R_AZ>(acc, c);
       const double bx = azy - ayz, by = axz - azx, bz = ayx - axy;
       const double rho1 = exp(-lnrho);
       const double t0 = bx * c.dx_1, t1 = by * c.dy_1, t2 = bz * c.dz_1;

@@ -256,6 +256,17 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   h.fx1 = h.dx_1 / 60.0; h.fy1 = h.dy_1 / 60.0; h.fz1 = h.dz_1 / 60.0;
   h.fx2 = h.dx_1 * h.dx_1; h.fy2 = h.dy_1 * h.dy_1; h.fz2 = h.dz_1 * h.dz_1;
   h.fxy = h.dx_1 * h.dy_1 / 720.0; h.fyz = h.dy_1 * h.dz_1 / 720.0; h.fzx = h.dz_1 * h.dx_1 / 720.0;
+  {
+    const double c1[3] = {45.0, -9.0, 1.0}, c2[4] = {-490.0 / 180.0, 270.0 / 180.0, -27.0 / 180.0, 2.0 / 180.0}, cm[3] = {270.0, -27.0, 2.0};
+    for (int i = 0; i < 3; i++) { h.k1x[i] = h.fx1 * c1[i]; h.k1y[i] = h.fy1 * c1[i]; h.k1z[i] = h.fz1 * c1[i];
+                                  h.kxy[i] = h.fxy * cm[i]; h.kyz[i] = h.fyz * cm[i]; h.kzx[i] = h.fzx * cm[i]; }
+    for (int i = 0; i < 4; i++) { h.k2x[i] = h.fx2 * c2[i]; h.k2y[i] = h.fy2 * c2[i]; h.k2z[i] = h.fz2 * c2[i]; }
+    for (int i = 0; i < 3; i++) {
+      h.dlyu[i][0] = h.nu / 3.0 * cm[i] * h.fzx; h.dlyu[i][1] = h.nu / 3.0 * cm[i] * h.fyz;
+      h.dlya[i][0] = h.mu01 * cm[i] * h.fzx;     h.dlya[i][1] = h.mu01 * cm[i] * h.fyz;
+    }
+    h.k2yz0 = h.k2y[0] + h.k2z[0]; h.k2zx0 = h.k2z[0] + h.k2x[0]; h.k2xy0 = h.k2x[0] + h.k2y[0]; h.k2xyz0 = h.k2x[0] + h.k2y[0] + h.k2z[0];
+  }
   g.nelem = (size_t)h.mw * P.mvar;
   if (realloc) {
     free_fields();

@@ -91,6 +91,7 @@ template <bool MAG, bool ENT> struct DlyCfg {
 // register window; the z-mixed accessors return 0 (those terms are completed in phase B)
 template <bool MAG, bool ENT>
 struct DlyAcc {
+  static constexpr bool PS = true;
   PC_DEV constexpr bool bidiag() const { return true; }
   const double *smem0;
   unsigned cb;            // byte offset of this thread's cell in the ring slot of the centre plane
@@ -111,17 +112,14 @@ struct DlyAcc {
 template <bool MAG, bool ENT, int K>
 PC_DEV void dly_combos(const DlyAcc<MAG, ENT> &a, const DevPar &c, double *__restrict__ d)
 {
-  const double ck = K == 1 ? 270.0 : (K == 2 ? -27.0 : 2.0);
-  const double third = 1.0 / 3.0;
-  const double sx = ck * c.fzx, sy = ck * c.fyz;
-  const double vu = c.nu * third;
-  d[0] = (vu * sx) * a.template dx<R_UZ, K>();                                   // nu/3 dxz(uz)
-  d[1] = (vu * sy) * a.template dy<R_UZ, K>();                                   // nu/3 dyz(uz)
-  d[2] = vu * (sx * a.template dx<R_UX, K>() + sy * a.template dy<R_UY, K>());   // nu/3 (dxz(ux) + dyz(uy))
+  const double *su = c.dlyu[K - 1], *sa = c.dlya[K - 1];      // nu/3*c_K*{fzx,fyz}, mu01*c_K*{fzx,fyz}
+  d[0] = su[0] * a.template dx<R_UZ, K>();                                           // nu/3 dxz(uz)
+  d[1] = su[1] * a.template dy<R_UZ, K>();                                           // nu/3 dyz(uz)
+  d[2] = fma(su[0], a.template dx<R_UX, K>(), su[1] * a.template dy<R_UY, K>());     // nu/3 (dxz(ux) + dyz(uy))
   if (MAG) {
-    d[3] = (c.mu01 * sx) * a.template dx<R_AZ, K>();                             // Jm_x = mu01 dxz(Az)
-    d[4] = (c.mu01 * sy) * a.template dy<R_AZ, K>();                             // Jm_y = mu01 dyz(Az)
-    d[5] = c.mu01 * (sx * a.template dx<R_AX, K>() + sy * a.template dy<R_AY, K>());   // Jm_z
+    d[3] = sa[0] * a.template dx<R_AZ, K>();                                         // Jm_x = mu01 dxz(Az)
+    d[4] = sa[1] * a.template dy<R_AZ, K>();                                         // Jm_y = mu01 dyz(Az)
+    d[5] = fma(sa[0], a.template dx<R_AX, K>(), sa[1] * a.template dy<R_AY, K>());   // Jm_z
   }
 }
 
