@@ -41,6 +41,9 @@ struct SubstepArgs {
   double *partials;   // [nblocks][NRED] when AUXM>0
   int z_lo, z_hi;     // range of output planes (interior-relative, [z_lo,z_hi))
   int zchunk;
+  // tile sub-range of a launch (x/y face exchange overlapped with interior tiles): the CTA's tile is
+  // (tx0 + blockIdx.x*txs, ty0 + blockIdx.y*tys); ntx/nty = grid extent (0 = all tiles)
+  int tx0, txs, ntx, ty0, tys, nty;
 };
 
 // ------------------------------------------------------------------------
@@ -653,7 +656,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
   constexpr bool WPF = PCB200_WPF;     // old 2N register: L2 prefetch + late load instead of an early load held in registers
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx;
-  const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
+  const int x0 = (a.tx0 + blockIdx.x * a.txs) * TX, y0 = (a.ty0 + blockIdx.y * a.tys) * TY;
   const int zb = a.z_lo + blockIdx.z * a.zchunk;
   const int ze = min(zb + a.zchunk, a.z_hi);
   const bool active = (x0 + tx < c.nx) && (y0 + ty < c.ny);

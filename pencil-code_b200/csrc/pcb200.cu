@@ -70,6 +70,8 @@ struct Ctx {
   bool use_dly = true;          // rhs_dly (delayed z-mixed terms, tensor-memory history); PCB200_KERNEL=tma selects rhs_tma
   int zchunk = 0;
   const char *kname = "";        // kernel of the last substep launch
+  cudaStream_t bcs = nullptr;   // stream of the ghost-zone work (compute stream, or the comm stream while it overlaps interior tiles)
+  int overlap_force = -1;       // PCB200_OVERLAP_XY: 1/0 force the x/y overlap on/off, unset = when >= 2 directions are decomposed
   bool zsplit = false;          // PCB200_ZSPLIT=1: interior planes overlap with the z halo exchange (3 launches per substep); default: wait for the halo, one launch -- faster since the kernels got shorter (28.4 vs 28.9 ms/step on 2 GPUs)
   bool use_prepass = true;      // isothermal runs: CFL pre-pass + fused update in substep 1 (PCB200_PREPASS=0: axpy pass)
   int zchunk_dly = 0;           // rhs_dly pays 6 extra steps per chunk: fewer, longer chunks
@@ -141,6 +143,9 @@ extern "C" int pcb200_init(int local_rank)
     g.use_prepass = !pp || atoi(pp) != 0;
     const char *zs = getenv("PCB200_ZSPLIT");
     g.zsplit = zs && atoi(zs) != 0;
+    const char *ov = getenv("PCB200_OVERLAP_XY");
+    g.overlap_force = ov ? (atoi(ov) != 0) : -1;
+    g.bcs = g.st;
     const char *t = getenv("PCB200_TIME_RHS");
     g.time_rhs = t && atoi(t) != 0;
     g.inited = true;
@@ -157,6 +162,20 @@ static void free_fields()
 }
 
 // TMA descriptors: f seen as a 3-D tensor (mx, my, mz*mvar) of doubles, box {HX,HY,1}.
+// rhs_dly: one CTA per SM, a chunk of zc planes takes zc+6 steps (+ ~6 steps of start-up latency);
+// pick the chunk length that minimises waves x steps
+static int dly_chunk(int tiles, int nz)
+{
+  int best = nz; double bestc = 1e30;
+  for (int nch = 1; nch <= 64 && (nz + nch - 1) / nch >= 16; nch++) {
+    const int z = (nz + nch - 1) / nch;
+    const double waves = ceil((double)tiles * nch / 148.0);
+    const double cost = waves * (z + 12);
+    if (cost < bestc * 0.999) { bestc = cost; best = z; }
+  }
+  return best;
+}
+
 // cuTensorMapEncodeTiled is taken from the driver at run time (no -lcuda).
 static int make_tensor_maps()
 {
@@ -304,24 +323,16 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
     const char *e = getenv("PCB200_ZCHUNK");
     if (e && atoi(e) > 0) zc = atoi(e);
     g.zchunk = zc;
-    // rhs_dly: one CTA per SM, a chunk of zc planes takes zc+6 steps (+ ~6 steps of start-up latency);
-    // pick the chunk length that minimises waves x steps
-    int best = P.nz; double bestc = 1e30;
-    for (int nch = 1; nch <= 64 && (P.nz + nch - 1) / nch >= 16; nch++) {
-      const int z = (P.nz + nch - 1) / nch;
-      const double waves = ceil((double)tiles * nch / 148.0);
-      const double cost = waves * (z + 12);
-      if (cost < bestc * 0.999) { bestc = cost; best = z; }
-    }
-    if (e && atoi(e) > 0) best = atoi(e);
-    g.zchunk_dly = best;
+    g.zchunk_dly = dly_chunk(tiles, P.nz);
+    if (e && atoi(e) > 0) g.zchunk_dly = atoi(e);
   }
   {
     const int zcmin = g.zchunk < g.zchunk_dly ? g.zchunk : g.zchunk_dly;
     const size_t nb_m = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + zcmin - 1) / zcmin + 2);
     const size_t nb_g = (size_t)((P.nx + 31) / 32) * ((P.ny + 3) / 4) * ((P.nz + 1) / 2 + 2);
     const size_t nb_p = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + 63) / 64);   // cfl_prepass
-    const size_t need = std::max(std::max(nb_m, nb_g), nb_p) * NRED;
+    const size_t nb_s = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * 70;                  // split launches, up to 64 chunks each
+    const size_t need = std::max(std::max(std::max(nb_m, nb_g), nb_p), nb_s) * NRED;
     if (need > g.npartials) { if (g.partials) cudaFree(g.partials); CK(cudaMalloc(&g.partials, need * sizeof(double))); g.npartials = need; }
   }
   CK(cudaMemcpyToSymbolAsync(c_par, &h, sizeof(DevPar), 0, cudaMemcpyHostToDevice, g.st));
@@ -436,7 +447,7 @@ static int launch_bc(double *f, int axis, int do_lo, int do_hi)
   const int mm[3] = {h.mx, h.my, h.mz};
   const int nb = axis == 0 ? mm[1] : mm[0], nc = axis == 2 ? mm[1] : mm[2];
   dim3 blk(128), grd((nb + 127) / 128, nc);
-  bc_fill<<<grd, blk, 0, g.st>>>(b);
+  bc_fill<<<grd, blk, 0, g.bcs>>>(b);
   g.launches++;
   CK(cudaGetLastError());
   return PCB200_OK;
@@ -459,7 +470,7 @@ static int launch_bc_periodic(double *f, bool wx, bool wy, bool wz)
   b.n0 = wx ? 6LL * h.my * h.mz : 0; b.n1 = wy ? 6LL * h.mx * h.mz : 0; b.n2 = wz ? 6LL * h.mx * h.my : 0;
   const long long n = b.n0 + b.n1 + b.n2;
   dim3 blk(256), grd((unsigned)((n + 255) / 256), P.mvar);
-  bc_periodic<<<grd, blk, 0, g.st>>>(b);
+  bc_periodic<<<grd, blk, 0, g.bcs>>>(b);
   g.launches++;
   CK(cudaGetLastError());
   return PCB200_OK;
@@ -512,17 +523,17 @@ static int exchange_packed(double *f, int axis)
   dim3 blk(256), grd((unsigned)((per_var + 255) / 256), P.mvar);
   auto copy = [&](double *buf, int start, int unpack) {
     FaceArgs a; a.f = f; a.buf = buf; a.axis = axis; a.start = start; a.unpack = unpack; a.nplanes = NG;
-    face_copy<<<grd, blk, 0, g.st>>>(a);
+    face_copy<<<grd, blk, 0, g.bcs>>>(a);
     g.launches++;
   };
   if (nlo >= 0) copy(g.face[0], NG, 0);          // lowest interior planes
   if (nhi >= 0) copy(g.face[1], n, 0);           // highest interior planes
   CK(cudaGetLastError());
   NK(g.nccl.GroupStart());
-  if (nlo >= 0) NK(g.nccl.Send(g.face[0], cnt, 8, nlo, g.comm, g.st));
-  if (nhi >= 0) NK(g.nccl.Recv(g.face[3], cnt, 8, nhi, g.comm, g.st));
-  if (nhi >= 0) NK(g.nccl.Send(g.face[1], cnt, 8, nhi, g.comm, g.st));
-  if (nlo >= 0) NK(g.nccl.Recv(g.face[2], cnt, 8, nlo, g.comm, g.st));
+  if (nlo >= 0) NK(g.nccl.Send(g.face[0], cnt, 8, nlo, g.comm, g.bcs));
+  if (nhi >= 0) NK(g.nccl.Recv(g.face[3], cnt, 8, nhi, g.comm, g.bcs));
+  if (nhi >= 0) NK(g.nccl.Send(g.face[1], cnt, 8, nhi, g.comm, g.bcs));
+  if (nlo >= 0) NK(g.nccl.Recv(g.face[2], cnt, 8, nlo, g.comm, g.bcs));
   NK(g.nccl.GroupEnd());
   if (nhi >= 0) copy(g.face[3], NG + n, 1);      // upper ghosts
   if (nlo >= 0) copy(g.face[2], 0, 1);           // lower ghosts
@@ -550,8 +561,12 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     else if (E) rhs_global<false, true, AUXM><<<grd, blk, 0, g.st>>>(a);
     else rhs_global<false, false, AUXM><<<grd, blk, 0, g.st>>>(a);
   } else if (g.have_tma && !g.use_cpasync) {
+    const int ntx_all = (P.nx + TX - 1) / TX, nty_all = (P.ny + TY - 1) / TY;
+    const bool sub = a.ntx > 0;                 // tile sub-range (x/y overlap)
+    if (!sub) { a.tx0 = 0; a.txs = 1; a.ntx = ntx_all; a.ty0 = 0; a.tys = 1; a.nty = nty_all; }
     a.zchunk = g.zchunk < (z_hi - z_lo) ? g.zchunk : (z_hi - z_lo);
-    dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
+    if (sub) { const int zc = dly_chunk(a.ntx * a.nty, z_hi - z_lo); a.zchunk = zc < a.zchunk ? zc : a.zchunk; }
+    dim3 blk(TX, TY), grd(a.ntx, a.nty, (z_hi - z_lo + a.zchunk - 1) / a.zchunk);
     *nblocks_out = grd.x * grd.y * grd.z;
     const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
     const bool rw = a.alpha != 0.0;
@@ -559,7 +574,8 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     if (g.use_dly && g.have_dly && P.lbidiagonal_derij && AUXM < 2 && !E) {
       const CUtensorMap &tm4 = g.tmap4[a.f_in == g.f[0] ? 0 : 1];
       g.kname = "rhs_dly";
-      a.zchunk = g.zchunk_dly < (z_hi - z_lo) ? g.zchunk_dly : (z_hi - z_lo);
+      a.zchunk = sub ? dly_chunk(a.ntx * a.nty, z_hi - z_lo) : g.zchunk_dly;
+      if (a.zchunk > z_hi - z_lo) a.zchunk = z_hi - z_lo;
       grd.z = (z_hi - z_lo + a.zchunk - 1) / a.zchunk;
       *nblocks_out = grd.x * grd.y * grd.z;
       // centre-plane-only stencils, z-mixed terms finished three planes late from tensor memory
@@ -949,7 +965,29 @@ static int do_substep(int isub, int ldiagnos)
     pend[0] = pend[1] = pend[2] = false;
     return r;
   };
-  const bool multi = np[2] > 1;          // z decomposed: interior planes overlap with the z exchange
+  const bool multi = np[2] > 1;          // z decomposed
+  const bool first = isub == 1;
+  const bool need_dt = first && P.ldt;
+  // Isothermal runs: dt from a light CFL pre-pass over the start-of-step state, so that substep 1
+  // applies the 2N update itself and the separate axpy pass over f and w disappears.
+  const bool prepass = need_dt && !ldiagnos && !P.lentropy && g.use_prepass;
+  // x/y-decomposed runs: the whole ghost-zone sequence (boundary conditions, packed x/y faces, z
+  // planes) runs on the comm stream while the compute stream works on the tiles that need no ghost
+  // cell; the boundary shell (first/last tile column and row, first/last NG planes) follows
+  // (initiate_isendrcv_bdry / finalize_isendrcv_bdry, mpicomm.f90:1325-2047).  Not in the substep
+  // that starts with the CFL pre-pass (it needs the ghost zones at once).
+  const int ntx = (P.nx + TX - 1) / TX, nty = (P.ny + TY - 1) / TY;
+  // pays when at least two directions are decomposed (measured on 2 GPUs, x split only: the exchange costs
+  // 0.37 ms per substep, the five launches of the split 0.8 ms); PCB200_OVERLAP_XY=1/0 forces it on/off
+  const int ndec = (np[0] > 1) + (np[1] > 1) + (np[2] > 1);
+  const bool ovl_want = g.overlap_force >= 0 ? g.overlap_force != 0 : ndec >= 2;
+  const bool ovl = (np[0] > 1 || np[1] > 1) && !g.part.on && !prepass && g.have_tma && !g.use_global &&
+                   !g.use_cpasync && ntx >= 3 && nty >= 3 && P.nz >= 3 * NG + 2 && ovl_want;
+  if (ovl) {
+    CK(cudaEventRecord(g.ev_bc, g.st));
+    CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0));
+    g.bcs = g.st_comm;
+  }
   for (int axis = 0; axis < 3; axis++) {
     if (np[axis] == 1) {
       if (wraps_locally(axis)) { pend[axis] = true; continue; }
@@ -965,16 +1003,14 @@ static int do_substep(int isub, int ldiagnos)
       if (lo || hi) if ((rc = launch_bc(fin, axis, lo, hi))) return rc;
       if ((rc = exchange_packed(fin, axis))) return rc;
     } else {
-      CK(cudaEventRecord(g.ev_bc, g.st));
-      CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0));
+      if (!ovl) { CK(cudaEventRecord(g.ev_bc, g.st)); CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0)); }
       if ((rc = exchange_z(fin))) return rc;
-      CK(cudaEventRecord(g.ev_halo, g.st_comm));
+      if (!ovl) CK(cudaEventRecord(g.ev_halo, g.st_comm));
       if (lo || hi) if ((rc = launch_bc(fin, 2, lo, hi))) return rc;
     }
   }
   if ((rc = flush())) return rc;
-  const bool first = isub == 1;
-  const bool need_dt = first && P.ldt;
+  if (ovl) { CK(cudaEventRecord(g.ev_halo, g.st_comm)); g.bcs = g.st; }
   const int auxm = first ? (ldiagnos ? 2 : (need_dt ? 1 : 0)) : 0;
   SubstepArgs a; memset(&a, 0, sizeof(a));
   a.f_in = fin; a.w = g.w; a.f_out = fout;
@@ -989,10 +1025,28 @@ static int do_substep(int isub, int ldiagnos)
     if ((rc = part_pencils(fin, need_dt))) return rc;
   }
   int nb0 = 0, nb1 = 0, nb2 = 0;
-  // Isothermal runs: dt from a light CFL pre-pass over the start-of-step state, so that substep 1
-  // applies the 2N update itself and the separate axpy pass over f and w disappears.
-  const bool prepass = need_dt && !ldiagnos && !P.lentropy && g.use_prepass;
-  if (prepass) {
+  if (ovl) {
+    int nb = 0; size_t off = 0;
+    // Boundary conditions 'a' and 'cT' also set the boundary plane itself (an interior cell), so the
+    // overlapped part keeps one more plane away from the z faces: it reads z-3 >= 1.
+    const int ZB = NG + 1;
+    SubstepArgs t = a;                   // tiles that touch no ghost cell
+    t.tx0 = 1; t.txs = 1; t.ntx = ntx - 2; t.ty0 = 1; t.tys = 1; t.nty = nty - 2;
+    if ((rc = launch_rhs(auxm, t, ZB, P.nz - ZB, off, &nb))) return rc;
+    off += nb;
+    CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0));
+    if ((rc = launch_rhs(auxm, a, 0, ZB, off, &nb))) return rc;                  // first and last ZB planes, all tiles
+    off += nb;
+    if ((rc = launch_rhs(auxm, a, P.nz - ZB, P.nz, off, &nb))) return rc;
+    off += nb;
+    t = a; t.tx0 = 0; t.txs = 1; t.ntx = ntx; t.ty0 = 0; t.tys = nty - 1; t.nty = 2;   // first and last tile row
+    if ((rc = launch_rhs(auxm, t, ZB, P.nz - ZB, off, &nb))) return rc;
+    off += nb;
+    t = a; t.tx0 = 0; t.txs = ntx - 1; t.ntx = 2; t.ty0 = 1; t.tys = 1; t.nty = nty - 2; // first and last tile column
+    if ((rc = launch_rhs(auxm, t, ZB, P.nz - ZB, off, &nb))) return rc;
+    off += nb;
+    nb0 = (int)off;
+  } else if (prepass) {
     if (multi) CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0));
     const int zc = 64;
     dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (P.nz + zc - 1) / zc);

@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   constexpr unsigned BOX_BYTES = NF * PE * 8;       // one plane of every field
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx, warp = tid >> 5;
-  const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
+  const int x0 = (a.tx0 + blockIdx.x * a.txs) * TX, y0 = (a.ty0 + blockIdx.y * a.tys) * TY;
   const int zb = a.z_lo + blockIdx.z * a.zchunk;
   const int ze = min(zb + a.zchunk, a.z_hi);
   const int nzc = ze - zb;

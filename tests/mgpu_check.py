@@ -31,16 +31,19 @@ def main():
     dev.comm_init(idt.numpy().tobytes(), rank, world)
     ok = True
     nsteps = 5
+    # global x,y size: 32 by default; PCB200_MGPU_NXY=208,48 gives >= 3 tile columns and rows per rank, which
+    # switches on the overlap of the x/y face exchange with the interior tiles (and has ragged edge tiles)
+    gx, gy = (int(v) for v in os.environ.get("PCB200_MGPU_NXY", "32,32").split(","))
     decomps = [(px, py, world // (px * py)) for px in (1, 2, 4, 8) for py in (1, 2, 4, 8)
-               if world % (px * py) == 0 and 32 // px >= 8 and 32 // py >= 8]
+               if world % (px * py) == 0 and gx // px >= 8 and gy // py >= 8]
     if os.environ.get("PCB200_NPROC"):
         decomps = [tuple(int(v) for v in os.environ["PCB200_NPROC"].split(","))]
     for nproc in decomps:
         gz = 16 * nproc[2]
         cases = {
-            "mhd_periodic": lambda npr, ipr: pk.setups.make_params(32, 32, gz, magnetic=True, nproc=npr, iproc=ipr,
+            "mhd_periodic": lambda npr, ipr: pk.setups.make_params(gx, gy, gz, magnetic=True, nproc=npr, iproc=ipr,
                                                                    nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3),
-            "convslab_walls": lambda npr, ipr: pk.setups.config_convslab(32, 32, gz, nproc=npr, iproc=ipr),
+            "convslab_walls": lambda npr, ipr: pk.setups.config_convslab(gx, gy, gz, nproc=npr, iproc=ipr),
         }
         for name, mk in cases.items():
             P, zprof, grid = mk(nproc, rank)

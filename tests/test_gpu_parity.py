@@ -186,6 +186,21 @@ def test_two_gpu_halo_exchange_matches_oracle():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+def test_two_gpu_xy_overlap_matches_oracle():
+    """x- and y-split on 2 GPUs with >= 3 tile columns/rows per rank: the ghost-zone sequence runs on the comm
+    stream while the interior tiles compute, boundary shell afterwards == single-domain oracle"""
+    import os, subprocess, sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PCB200_MGPU_NXY="208,48", PCB200_OVERLAP_XY="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29519", os.path.join(root, "tests", "mgpu_check.py")],
+                       capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_gpu_reproduces_convslab_reference_out_double(pk, dev):
     """the CUDA path itself against the REFERENCE's golden time series
     (samples/conv-slab/reference.out.double, real Fortran/MPI build, 13 digits)"""
