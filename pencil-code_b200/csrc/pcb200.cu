@@ -71,7 +71,7 @@ struct Ctx {
   int zchunk = 0;
   const char *kname = "";        // kernel of the last substep launch
   cudaStream_t bcs = nullptr;   // stream of the ghost-zone work (compute stream, or the comm stream while it overlaps interior tiles)
-  int overlap_force = -1;       // PCB200_OVERLAP_XY: 1/0 force the x/y overlap on/off, unset = when >= 2 directions are decomposed
+  int overlap_force = -1;       // PCB200_OVERLAP_XY=1: overlap the x/y face exchange with the interior tiles (off by default, see do_substep)
   bool zsplit = false;          // PCB200_ZSPLIT=1: interior planes overlap with the z halo exchange (3 launches per substep); default: wait for the halo, one launch -- faster since the kernels got shorter (28.4 vs 28.9 ms/step on 2 GPUs)
   bool use_prepass = true;      // isothermal runs: CFL pre-pass + fused update in substep 1 (PCB200_PREPASS=0: axpy pass)
   int zchunk_dly = 0;           // rhs_dly pays 6 extra steps per chunk: fewer, longer chunks
@@ -126,7 +126,13 @@ extern "C" int pcb200_init(int local_rank)
   CK(cudaSetDevice(g.dev));
   if (!g.inited) {
     CK(cudaStreamCreateWithFlags(&g.st, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&g.st_comm, cudaStreamNonBlocking));
+    {
+      // comm stream at the highest priority: its small pack/unpack/NCCL kernels must get an SM as soon as one
+      // frees up while the compute stream has thousands of one-CTA-per-SM blocks queued
+      int plo = 0, phi = 0;
+      CK(cudaDeviceGetStreamPriorityRange(&plo, &phi));
+      CK(cudaStreamCreateWithPriority(&g.st_comm, cudaStreamNonBlocking, phi));
+    }
     CK(cudaEventCreate(&g.ev_t0)); CK(cudaEventCreate(&g.ev_t1));
     CK(cudaEventCreate(&g.ev_k0)); CK(cudaEventCreate(&g.ev_k1));
     CK(cudaEventCreateWithFlags(&g.ev_bc, cudaEventDisableTiming));
@@ -977,10 +983,10 @@ static int do_substep(int isub, int ldiagnos)
   // (initiate_isendrcv_bdry / finalize_isendrcv_bdry, mpicomm.f90:1325-2047).  Not in the substep
   // that starts with the CFL pre-pass (it needs the ghost zones at once).
   const int ntx = (P.nx + TX - 1) / TX, nty = (P.ny + TY - 1) / TY;
-  // pays when at least two directions are decomposed (measured on 2 GPUs, x split only: the exchange costs
-  // 0.37 ms per substep, the five launches of the split 0.8 ms); PCB200_OVERLAP_XY=1/0 forces it on/off
-  const int ndec = (np[0] > 1) + (np[1] > 1) + (np[2] > 1);
-  const bool ovl_want = g.overlap_force >= 0 ? g.overlap_force != 0 : ndec >= 2;
+  // Off by default: measured slower than the sequential order (2 GPUs split in x: 29.3 vs 28.4 ms/step; 8 GPUs
+  // 2x2x2: 35.5 vs 34.3 ms/step) -- the compute kernel holds every SM with one 1-ms CTA each, so the small
+  // kernels of the comm stream do not start on time.  PCB200_OVERLAP_XY=1 switches it on.
+  const bool ovl_want = g.overlap_force > 0;
   const bool ovl = (np[0] > 1 || np[1] > 1) && !g.part.on && !prepass && g.have_tma && !g.use_global &&
                    !g.use_cpasync && ntx >= 3 && nty >= 3 && P.nz >= 3 * NG + 2 && ovl_want;
   if (ovl) {
