@@ -336,7 +336,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
     const int zcmin = g.zchunk < g.zchunk_dly ? g.zchunk : g.zchunk_dly;
     const size_t nb_m = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + zcmin - 1) / zcmin + 2);
     const size_t nb_g = (size_t)((P.nx + 31) / 32) * ((P.ny + 3) / 4) * ((P.nz + 1) / 2 + 2);
-    const size_t nb_p = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + 63) / 64);   // cfl_prepass
+    const size_t nb_p = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + 15) / 16);   // cfl_prepass
     const size_t nb_s = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * 70;                  // split launches, up to 64 chunks each
     const size_t need = std::max(std::max(std::max(nb_m, nb_g), nb_p), nb_s) * NRED;
     if (need > g.npartials) { if (g.partials) cudaFree(g.partials); CK(cudaMalloc(&g.partials, need * sizeof(double))); g.npartials = need; }
@@ -1054,7 +1054,8 @@ static int do_substep(int isub, int ldiagnos)
     nb0 = (int)off;
   } else if (prepass) {
     if (multi) CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0));
-    const int zc = 64;
+    const char *zce = getenv("PCB200_PREPASS_ZC");
+    const int zc = zce && atoi(zce) > 0 ? atoi(zce) : 64;
     dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (P.nz + zc - 1) / zc);
     if (P.lmagnetic) cfl_prepass<true><<<grd, blk, 0, g.st>>>(fin, g.partials, 0, P.nz, zc);
     else cfl_prepass<false><<<grd, blk, 0, g.st>>>(fin, g.partials, 0, P.nz, zc);
