@@ -139,6 +139,42 @@ def test_forcing_and_diagnostics(pk, orc, dev):
             assert abs(a[nm] - b[q]) <= 1e-11 * abs(b[q]) + atol, (nm, a[nm], b[q])
 
 
+def test_rhs_dly_matches_rhs_tma_and_axpy_path(tmp_path):
+    """The production path (rhs_dly + CFL pre-pass) against the library's other path (rhs_tma, CFL reduction in
+    substep 1 + axpy pass) on a ragged 72x40x44 MHD box, 20 steps, both as fresh processes (the kernel choice is
+    read once in pcb200_init): fields to 1e-12, dt sequence to 1e-13; and the kernel names are what they should be."""
+    import os, subprocess, sys
+    import numpy as np
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "import __graft_entry__ as e\n"
+        "pk = e.package()\n"
+        "P, zprof, grid = pk.setups.make_params(72, 40, 44, magnetic=True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3)\n"
+        "f = pk.setups.synthetic_fields(P, grid)\n"
+        "dev = pk.GPU(); dev.gpu_init(0); dev.initialize_GPU(P, zprof); dev.register_GPU(f)\n"
+        "dts = []\n"
+        "for it in range(20):\n"
+        "    for isub in (1, 2, 3):\n"
+        "        dt = dev.rhs_GPU(f, isub)\n"
+        "    dts.append(dt)\n"
+        "dev.copy_farray_from_GPU(f)\n"
+        "np.savez(sys.argv[1], f=f[:, 3:-3, 3:-3, 3:-3], dts=np.array(dts), kernel=dev.kernel_name())\n"
+    ) % root
+    out = {}
+    for name, env in (("dly", {}), ("tma", {"PCB200_KERNEL": "tma", "PCB200_PREPASS": "0"})):
+        path = str(tmp_path / (name + ".npz"))
+        r = subprocess.run([sys.executable, "-c", script, path], env=dict(os.environ, **env), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        out[name] = np.load(path)
+    assert str(out["dly"]["kernel"]) == "rhs_dly" and str(out["tma"]["kernel"]) == "rhs_tma"
+    a, b = out["dly"]["f"], out["tma"]["f"]
+    err = max(np.abs(a[k] - b[k]).max() / np.abs(b[k]).max() for k in range(a.shape[0]))
+    dterr = np.abs(out["dly"]["dts"] / out["tma"]["dts"] - 1).max()
+    assert err < 1e-12 and dterr < 1e-13, (err, dterr)
+
+
 def test_fixed_dt(pk, orc, dev):
     P, zprof, grid = pk.setups.config_mhd(32, ldt=0, dt_fixed=1e-3)
     f0 = pk.setups.synthetic_fields(P, grid)
