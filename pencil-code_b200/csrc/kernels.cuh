@@ -918,10 +918,11 @@ __global__ void __launch_bounds__(NTHR, 3) cfl_prepass(const double *__restrict_
       const double t0 = bx * c.dx_1, t1 = by * c.dy_1, t2 = bz * c.dz_1;
       advec_va2 = (t0 * t0 + t1 * t1 + t2 * t2) * c.mu01 * rho1;                            // magnetic.f90:5438
     }
+    // dt1 = sqrt((maxadvec/cdt)^2 + dt1_diffus^2) (equ.f90:1149) is a monotonic function of maxadvec (every
+    // step of it is monotonic in floating point too), so the maximum is taken over maxadvec and the
+    // function applied once per thread: same bits, one sqrt and one division less per cell
     const double maxadvec = advec_uu + sqrt(advec_va2 + advec_cs2);
-    const double dt1_advec = maxadvec / c.cdt;
-    const double dt1 = sqrt(dt1_advec * dt1_advec + dt1_diffus * dt1_diffus);             // equ.f90:1149
-    if (active) dt1max = fmax(dt1max, dt1);
+    if (active) dt1max = fmax(dt1max, maxadvec);
     if (!more) break;
     cp_async_wait_all();
     __syncthreads();
@@ -935,7 +936,10 @@ __global__ void __launch_bounds__(NTHR, 3) cfl_prepass(const double *__restrict_
   double red[NRED];
 #pragma unroll
   for (int q = 0; q < NRED; q++) red[q] = 0.0;
-  red[RD_DT1] = dt1max;
+  {
+    const double dt1_advec = dt1max / c.cdt;
+    red[RD_DT1] = sqrt(dt1_advec * dt1_advec + dt1_diffus * dt1_diffus);
+  }
   const int bl = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
   block_reduce_store<1>(red, tid, NTHR, redsm, partials, bl);
 }
