@@ -534,17 +534,19 @@ struct BcPerArgs { double *f; int wrap[3]; long long n0, n1, n2; };
 __global__ void bc_periodic(BcPerArgs b)
 {
   const DevPar &c = c_par;
-  long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // 32-bit index arithmetic (the three ghost shells have < 2^31 cells each; 64-bit divisions cost more than the copy)
+  unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned n0 = (unsigned)b.n0, n1 = (unsigned)b.n1, n2 = (unsigned)b.n2, mx = c.mx, my = c.my;
   int ix, iy, iz;
-  if (t < b.n0) {                                   // x ghosts: 6 x my x mz
-    const int gx = (int)(t % 6); const long long r = t / 6;
-    iy = (int)(r % c.my); iz = (int)(r / c.my); ix = gx < NG ? gx : c.nx + gx;
-  } else if ((t -= b.n0) < b.n1) {                  // y ghosts: mx x 6 x mz
-    ix = (int)(t % c.mx); const long long r = t / c.mx;
-    const int gy = (int)(r % 6); iz = (int)(r / 6); iy = gy < NG ? gy : c.ny + gy;
-  } else if ((t -= b.n1) < b.n2) {                  // z ghosts: mx x my x 6
-    ix = (int)(t % c.mx); const long long r = t / c.mx;
-    iy = (int)(r % c.my); const int gz = (int)(r / c.my); iz = gz < NG ? gz : c.nz + gz;
+  if (t < n0) {                                     // x ghosts: 6 x my x mz
+    const unsigned gx = t % 6u, r = t / 6u;
+    iy = (int)(r % my); iz = (int)(r / my); ix = gx < NG ? (int)gx : c.nx + (int)gx;
+  } else if ((t -= n0) < n1) {                      // y ghosts: mx x 6 x mz
+    ix = (int)(t % mx); const unsigned r = t / mx;
+    const unsigned gy = r % 6u; iz = (int)(r / 6u); iy = gy < NG ? (int)gy : c.ny + (int)gy;
+  } else if ((t -= n1) < n2) {                      // z ghosts: mx x my x 6
+    ix = (int)(t % mx); const unsigned r = t / mx;
+    iy = (int)(r % my); const unsigned gz = r / my; iz = gz < NG ? (int)gz : c.nz + (int)gz;
   } else return;
   const int sx = !b.wrap[0] ? ix : (ix < NG ? ix + c.nx : (ix >= NG + c.nx ? ix - c.nx : ix));
   const int sy = !b.wrap[1] ? iy : (iy < NG ? iy + c.ny : (iy >= NG + c.ny ? iy - c.ny : iy));
