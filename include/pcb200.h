@@ -263,7 +263,7 @@ int pcb200_particles_get_aux(double *np, double *rhop);
 
 /* name of the fused RHS+RK kernel of the last substep launch ("rhs_dly", "rhs_tma", "rhs_march",
  * "rhs_global"; "" before the first launch).  Selection: PCB200_KERNEL={dly,tma,cpasync,global};
- * default rhs_dly where it applies (lbidiagonal_derij=T, no entropy, no full-diagnostics substep). */
+ * default rhs_dly where it applies (lbidiagonal_derij=T, not magnetic+entropy, no full-diagnostics substep). */
 const char *pcb200_kernel_name(void);
 const char *pcb200_last_error(void);
 int pcb200_abi_version(void);

@@ -358,7 +358,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
 #define OPTIND(M, E) CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
                      CK(cudaFuncSetAttribute(rhs_dly<M, E, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
                      CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM))
-  OPTIND(false, false); OPTIND(true, false);
+  OPTIND(false, false); OPTIND(true, false); OPTIND(false, true);
 #undef OPTIND
   CK(cudaStreamSynchronize(g.st));
   g.have_par = true;
@@ -577,7 +577,7 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
     const bool rw = a.alpha != 0.0;
     g.kname = "rhs_tma";
-    if (g.use_dly && g.have_dly && P.lbidiagonal_derij && AUXM < 2 && !E) {
+    if (g.use_dly && g.have_dly && P.lbidiagonal_derij && AUXM < 2 && !(E && M)) {
       const CUtensorMap &tm4 = g.tmap4[a.f_in == g.f[0] ? 0 : 1];
       g.kname = "rhs_dly";
       a.zchunk = sub ? dly_chunk(a.ntx * a.nty, z_hi - z_lo) : g.zchunk_dly;
@@ -588,6 +588,8 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
       constexpr int AX = AUXM < 2 ? AUXM : 0;
       if (M) { if (rw) rhs_dly<true, false, 0, true><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
                else    rhs_dly<true, false, AX, false><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
+      else if (E) { if (rw) rhs_dly<false, true, 0, true><<<grd, blk, DlyCfg<false, true>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
+                    else    rhs_dly<false, true, AX, false><<<grd, blk, DlyCfg<false, true>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
       else   { if (rw) rhs_dly<false, false, 0, true><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
                else    rhs_dly<false, false, AX, false><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
     } else {

@@ -17,8 +17,9 @@
 // Shared memory holds 6 slots per field (centre .. centre+4 for the thread's
 // own z-column, +1 in flight) for all fields instead of 8 for six of them.
 //
-// Available for lbidiagonal_derij=T, AUXM<2 (the full 0-D diagnostics need |J|^2 at the
-// centre plane: those substeps use rhs_tma) and, with magnetic+entropy, lohmic_heat=F.
+// Used for lbidiagonal_derij=T, AUXM<2 (the full 0-D diagnostics need |J|^2 at the centre plane:
+// those substeps use rhs_tma), hydro / hydro+entropy / isothermal MHD.  Magnetic+entropy stays on
+// rhs_tma: Ohmic heating is quadratic in J and the pending state would not fit in tensor memory.
 #pragma once
 #include "kernels.cuh"
 #include <type_traits>
