@@ -23,6 +23,7 @@ def test_library_exports_every_declared_symbol(pk):
     assert set(pk.abi.SYMBOLS) == declared
     pk.abi.bind(lib)
     assert lib.pcb200_abi_version() == pk.abi.ABI_VERSION
+    assert lib.pcb200_kernel_name() == b""      # no substep launched yet (no compute call here: no GPU needed)
 
 
 def test_struct_layout_matches_c(pk, tmp_path):
