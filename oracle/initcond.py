@@ -108,3 +108,44 @@ def convslab_initial_condition(P, grid, *, cs0=0.57735, gamma=1.6666666, rho0=1.
     g = np.zeros_like(f)
     g[:, 3:-3, 3:-3, 3:-3] = f[:, 3:-3, 3:-3, 3:-3]
     return g
+
+
+# ---------------------------------------------------------------------------
+# samples/interlocked-fluxrings: initial_condition/fluxrings.f90
+# ---------------------------------------------------------------------------
+def _norm_ring(xx1, yy1, zz1, fring, Iring, R0, width):
+    """norm_ring, profile 'tanh' (initial_condition/fluxrings.f90:318-371): vector potential of a
+    canonical ring lying in the x-y plane."""
+    tmp = np.sqrt(xx1 ** 2 + yy1 ** 2) - R0
+    v3 = -fring * 0.5 * (1 + np.tanh(tmp / width)) * 0.5 / width / np.cosh(zz1 / width) ** 2
+    tmp = width - np.sqrt(tmp ** 2 + zz1 ** 2)
+    tmp = Iring * 0.5 * (1 + np.tanh(tmp / width))
+    phi = np.arctan2(yy1, xx1)
+    return -tmp * np.sin(phi), tmp * np.cos(phi), v3
+
+
+def fluxrings_initial_condition(P, grid, *, amplaa=1.0,
+                                rings=((1.0, 0.0, 1.0, 0.3, (0.0, 0.0, 1.0), (0.0, -0.5, 0.0)),
+                                       (1.0, 0.0, 1.0, 0.3, (1.0, 0.0, 0.0), (0.0, 0.5, 0.0)))):
+    """`fluxrings` (initial_condition/fluxrings.f90:205-298) with the parameters of
+    samples/interlocked-fluxrings/start.in: AA(x) = D AA0(D^-1 (x - disp)), D = rotation by phi about z
+    followed by theta about y.  uu=0, lnrho=0 (start.in sets no init for hydro/density).
+    rings: (fring, Iring, Rring, wr, axis, disp) per ring."""
+    x, y, z = grid["x"], grid["y"], grid["z"]
+    f = np.zeros((P.mvar, z.size, y.size, x.size))
+    X, Y, Z = x[None, None, :], y[None, :, None], z[:, None, None]
+    ia = P.iax - 1
+    for fring, Iring, R0, width, axis, disp in rings:
+        phi = math.atan2(axis[1], axis[0] + EPSI)
+        theta = math.atan2(math.sqrt(axis[0] ** 2 + axis[1] ** 2) + EPSI, axis[2])
+        ct, st, cp, sp = math.cos(theta), math.sin(theta), math.cos(phi), math.sin(phi)
+        xx1 = ct * cp * (X - disp[0]) + ct * sp * (Y - disp[1]) - st * (Z - disp[2])
+        yy1 = -sp * (X - disp[0]) + cp * (Y - disp[1]) + 0.0 * Z
+        zz1 = st * cp * (X - disp[0]) + st * sp * (Y - disp[1]) + ct * (Z - disp[2])
+        v1, v2, v3 = _norm_ring(xx1, yy1, zz1, fring, Iring, R0, width)
+        f[ia] += amplaa * (ct * cp * v1 - sp * v2 + st * cp * v3)
+        f[ia + 1] += amplaa * (ct * sp * v1 + cp * v2 + st * sp * v3)
+        f[ia + 2] += amplaa * (-st * v1 + ct * v3)
+    g = np.zeros_like(f)                     # start.x fills the interior only
+    g[:, 3:-3, 3:-3, 3:-3] = f[:, 3:-3, 3:-3, 3:-3]
+    return g

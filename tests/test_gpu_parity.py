@@ -313,3 +313,46 @@ def test_particles_match_oracle(pk, orc, dev, case):
     if "drag_only" not in case:
         # the back-reaction really acted on the gas: compare with a gas-only run
         assert pp.ldragforce_gas_par == 1
+
+
+def test_gpu_reproduces_fluxrings_reference_out_double(pk, dev):
+    """the CUDA path against the REFERENCE's golden time series of the headline physics
+    (samples/interlocked-fluxrings/reference.out.double: isothermal MHD, real Fortran/MPI build, 13 digits):
+    t, urms, umax, brms, bmax, jrms, jmax, abm, jbm at it = 0, 2, 4, 6, 8.  Tolerance 2e-11 as for conv-slab."""
+    from tests.test_oracle_fluxrings import compare_with_golden, fluxrings_setup, row_from_diag
+    P, zprof, grid, f = fluxrings_setup(pk)
+    dev.initialize_GPU(P, zprof)
+    dev.register_GPU(f)
+    t, rows = 0.0, []
+    for it in range(9):
+        for isub in (1, 2, 3):
+            dt = dev.rhs_GPU(f, isub, ldiagnos=(isub == 1 and it % 2 == 0))
+        if it % 2 == 0:
+            n = dev.diagnostics()
+            rows.append(row_from_diag(pk, P, it, t, [n[k] for k in pk.abi.DIAG_NAMES]))
+        t += dt
+    worst = compare_with_golden(np.array(rows))
+    print("GPU vs interlocked-fluxrings reference.out.double: worst rel", worst)
+
+
+# ---------------------------------------------------------------------------
+# production-size launch shapes (the benchmarked 16x64 tile grid, several z-chunks, element offsets ~1e9)
+PROD_CASES = {
+    # 512x512x64 isothermal MHD: the BENCH tile grid (16 x 64 tiles) with real z-chunking
+    "mhd_512x512x64": lambda pk: pk.setups.make_params(512, 512, 64, magnetic=True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3),
+    # 256^3 hydro (BASELINE config 2 shape)
+    "hydro_256": lambda pk: pk.setups.config_hydro(256),
+    # MHD + entropy at the full 518-wide tile row (config 4 physics)
+    "mhd_entropy_512x64x32": lambda pk: pk.setups.make_params(512, 64, 32, magnetic=True, entropy=True, nu=5e-3, eta=5e-3,
+                                                              cdt=0.4, cdtv=0.3, chi=1e-4, iheatcond=pk.abi.HCOND["chi-const"]),
+}
+
+
+@pytest.mark.parametrize("case", list(PROD_CASES))
+def test_production_size_one_step_matches_oracle(pk, orc, dev, case):
+    P, zprof, grid = PROD_CASES[case](pk)
+    f0 = pk.setups.synthetic_fields(P, grid)
+    fg, dtg, _ = run_gpu(dev, P, zprof, f0, 1)
+    fo, dto, _ = run_oracle(orc, P, zprof, f0, 1)
+    assert abs(dtg[0] - dto[0]) <= 1e-13 * dto[0]
+    assert relerr(fg, fo) < 1e-12
