@@ -1,0 +1,11 @@
+#!/bin/bash
+# usage: tools/gpu_retry.sh <logfile> <gpurun args...>
+# Retries a gpurun call while the pod answers "busy" (exit 3 / status=transient: nothing charged).
+log=$1; shift
+for i in $(seq 1 30); do
+  /usr/local/graft/bin/gpurun "$@" > "$log" 2>&1
+  rc=$?
+  if [ $rc -ne 3 ] && ! grep -q "status=transient" "$log"; then exit $rc; fi
+  sleep 120
+done
+exit 3
