@@ -35,6 +35,16 @@ void pcref_set_zprofile(int which, const double *prof, int nz)
   g_zprof_n[which] = nz;
 }
 
+/* bench.py --impl reference under torchrun inherits OMP_NUM_THREADS=1: the CPU arm sets the count itself */
+void pcref_set_num_threads(int n)
+{
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int pcref_num_threads(void)
 {
 #ifdef _OPENMP
@@ -361,6 +371,10 @@ static void rhs_point(const double *f, double *df, const pcb200_params *par,
     TT1 = exp(-lnTT);
     for (int j = 0; j < 3; j++) glnTT[j] = gamma_m1 * glnrho[j] + cv1 * gss[j];
     del2lnTT = gamma_m1 * del2lnrho + cv1 * del2ss;
+  } else if (gamma_m1 != 0.0) {
+    /* noentropy with gamma /= 1 selects the ISENTROPIC eos (noentropy.f90:113-116: select_eos_variable('ss',-1));
+     * leos_isentropic branch of calc_pencils_eos, eos_idealgas.f90:809-815 */
+    cs2 = par->cs20 * exp(gamma_m1 * (lnrho - par->lnrho0));
   }
 
   /* ---- calc_pencils_energy: entropy.f90:3165-3240 / noentropy.f90:255-313 ---- */

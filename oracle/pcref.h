@@ -67,6 +67,7 @@ void pcref_timestep(double *f, double *df, const pcb200_params *par,
 void pcref_addforce(double *f, const pcb200_params *par, const pcb200_forcing *frc);
 
 int pcref_num_threads(void);
+void pcref_set_num_threads(int n);
 
 /* ---- dust particles (pcref_particles.c; parity unpinned, see its header) ---- */
 void pcref_particles_boundconds(double *fp, const pcb200_params *par, const pcb200_particle_params *pp);

@@ -18,12 +18,27 @@ def build(force=False):
     return LIB
 
 
+FAST_LIB = os.path.join(_HERE, "libpcref_fast.so")
+
+
+def build_fast():
+    """-O3 -march=native build for TIMING the CPU arm (bench.py); compiled on the machine that runs it.
+    Returns None when it cannot be built (the caller then times the checker build and says so)."""
+    try:
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "fast"])
+        return FAST_LIB
+    except Exception:
+        return None
+
+
 class Oracle:
-    def __init__(self, abi):
-        """abi: the product's ctypes module (only for the shared struct layout)."""
+    def __init__(self, abi, lib_path=None):
+        """abi: the product's ctypes module (only for the shared struct layout).
+        lib_path: another build of the same sources (bench.py's timing build)."""
         build()
         self.abi = abi
-        L = self.lib = C.CDLL(LIB)
+        self.lib_path = lib_path or LIB
+        L = self.lib = C.CDLL(self.lib_path)
         d, i, p = C.c_double, C.c_int, C.c_void_p
         for name in ("pcref_der_field", "pcref_der2_field", "pcref_der6_field"):
             getattr(L, name).argtypes = [p, i, i, i, i, d, p]
@@ -43,6 +58,8 @@ class Oracle:
         L.pcref_set_zprofile.argtypes = [i, p, i]
         L.pcref_set_zprofile.restype = None
         L.pcref_num_threads.restype = i
+        L.pcref_set_num_threads.argtypes = [i]
+        L.pcref_set_num_threads.restype = None
         PP, PA = C.POINTER(abi.ParticleParams), C.POINTER(abi.Params)
         L.pcref_particles_boundconds.argtypes = [p, PA, PP]
         L.pcref_particles_map_nearest_grid.argtypes = [p, p, PA, PP]
@@ -105,6 +122,9 @@ class Oracle:
 
     def num_threads(self):
         return self.lib.pcref_num_threads()
+
+    def set_num_threads(self, n):
+        self.lib.pcref_set_num_threads(int(n))
 
     # ---- dust particles (pcref_particles.c) ----------------------------------
     def imn_array(self, par):

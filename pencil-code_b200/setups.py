@@ -278,3 +278,48 @@ def synthetic_particles(P, pp, seed=4321, vampl=0.05, block_only=False):
         st.fp[3 + j, :n] = vampl * rng.standard_normal(n)
     st.ipar[:n] = np.arange(1, n + 1, dtype=np.int32) + (iproc * n if block_only else 0)
     return st
+
+
+# ---------------------------------------------------------------------------
+# helical forcing coefficients (host side of forcing_hel; the random draws stay on the host)
+def forcing_shell(kmin=4.5, kmax=5.5):
+    """integer wave vectors with kmin <= |k| < kmax: what samples/helical-MHDturb/k.dat lists for kav=5"""
+    r = int(math.ceil(kmax))
+    ks = [(kx, ky, kz) for kx in range(-r, r + 1) for ky in range(-r, r + 1) for kz in range(-r, r + 1)
+          if kmin <= math.sqrt(kx * kx + ky * ky + kz * kz) < kmax]
+    return np.array(ks, dtype=np.float64)
+
+
+def helical_forcing_coefs(kvec, phase, phi, dt, *, force=0.07, relhel=1.0, kav=5.0, cs0eff=1.0, slope_ff=0.0):
+    """fconst_coefs_hel (forcing.f90:1554-1760) for one wave vector, phase and e-vector angle phi (the three random
+    numbers of a step), default switches (no shear, no k scaling, lhelical_test=F): returns abi.Forcing.
+    f_u += Re[(coef1 + i coef2) exp(i(k.x + phase))] * fact,  fact = force/ffnorm*sqrt(dt)  (forcing.f90:1741)."""
+    kx, ky, kz = (float(v) for v in kvec)
+    k2 = kx * kx + ky * ky + kz * kz
+    k = math.sqrt(k2)
+    ee = np.array([0.0, 1.0, 0.0]) if (ky == 0 and kz == 0) else np.array([1.0, 0.0, 0.0])   # forcing.f90:1651-1655
+    kk = np.array([kx, ky, kz])
+    e1 = np.cross(kk, ee); e1 /= math.sqrt(e1 @ e1)
+    e2 = np.cross(kk, e1); e2 /= math.sqrt(e2 @ e2)
+    ee = math.cos(phi) * e1 + math.sin(phi) * e2                                            # :1667-1675
+    kde = float(kk @ ee)
+    ke = np.cross(kk, ee)
+    kke = np.cross(kk, ke)
+    ffnorm = math.sqrt(1.0 + relhel ** 2) * k * math.sqrt(k2 - kde ** 2) / math.sqrt(kav * cs0eff ** 3) * (k / kav) ** slope_ff
+    frc = abi.Forcing()
+    for j in range(3):
+        frc.coef1[j] = k * ke[j]
+        frc.coef2[j] = relhel * kke[j]
+        frc.fda[j] = 1.0
+        frc.kk[j] = kk[j]
+    frc.phase = phase
+    frc.fact = force / ffnorm * math.sqrt(dt)
+    return frc
+
+
+def forcing_sequence(nsteps, seed=777):
+    """a recorded (k, phase, phi) sequence for bench.py --forcing (numpy generator, fixed seed: synthetic, not the
+    reference's nr_f90 stream)"""
+    rng = np.random.default_rng(seed)
+    shell = forcing_shell()
+    return [(shell[int(rng.integers(len(shell)))], math.pi * (2 * rng.random() - 1), 2 * math.pi * rng.random()) for _ in range(nsteps)]

@@ -356,3 +356,28 @@ def test_production_size_one_step_matches_oracle(pk, orc, dev, case):
     fo, dto, _ = run_oracle(orc, P, zprof, f0, 1)
     assert abs(dtg[0] - dto[0]) <= 1e-13 * dto[0]
     assert relerr(fg, fo) < 1e-12
+
+
+def test_c_driver_replays_host_sequence(pk, dev, tmp_path):
+    """tests/abi_driver.c (plain C, dlopen, no Python) replays what the Fortran host does -- init, initialize, register,
+    [substep x 3] x N with lvery_first, copy_farray, finalize -- and fills pcb200_params field by field from pcb200.h.
+    The same input through the Python mirror of the Fortran module (struct built by setups.make_params) must give
+    bit-identical dt and f: same library, same inputs; a difference means the two sides disagree about the ABI."""
+    import os, subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe, out = str(tmp_path / "abi_driver"), str(tmp_path / "out.bin")
+    subprocess.check_call(["/usr/bin/gcc", "-O1", "-I", os.path.join(root, "include"), os.path.join(root, "tests", "abi_driver.c"),
+                           "-o", exe, "-ldl", "-lm"])
+    n, nsteps = 32, 4
+    r = subprocess.run([exe, pk.gpu.LIB_PATH, str(n), str(nsteps), out], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    raw = open(out, "rb").read()
+    hdr = np.frombuffer(raw, dtype=np.int32, count=3)
+    assert list(hdr) == [n, nsteps, 7]
+    body = np.frombuffer(raw, dtype=np.float64, offset=12)
+    m = n + 6
+    dts_c, f0, f_c = body[:nsteps], body[nsteps:nsteps + 7 * m ** 3].reshape(7, m, m, m), body[nsteps + 7 * m ** 3:].reshape(7, m, m, m)
+    P, zprof, grid = pk.setups.config_mhd(n)
+    f_py, dts_py, _ = run_gpu(dev, P, zprof, np.ascontiguousarray(f0), nsteps)
+    assert np.array_equal(dts_c, dts_py), (dts_c, dts_py)
+    assert np.array_equal(f_c[INT], f_py[INT])
