@@ -268,6 +268,22 @@ const char *pcb200_kernel_name(void);
 const char *pcb200_last_error(void);
 int pcb200_abi_version(void);
 
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * CFL time step of a device-resident state -- the same cfl_prepass kernel that substep 1 of an
+ * isothermal run launches -- with the per-block partial maxima in a file-scope device array instead
+ * of allocated scratch.  Calls no cudaMalloc/cudaFree or allocating library routine.
+ *   f_dev       device pointer (16-byte aligned) to f(mx,my,mz,mvar) of the grid given to
+ *               pcb200_initialize, ghost zones already valid; read only
+ *   dt_out_dev  device pointer to two doubles: [0] = dt, [1] = 1/dt = max(dt1_max, 1/dtmax) of THIS
+ *               rank (no cross-rank maximum, no particle terms)
+ * Asynchronous on the library's compute stream (pcb200_sync() waits).  Limit: at most
+ * PCB200_NOALLOC_MAX_BLOCKS blocks of 32x8x64 cells (512^3 cells per rank; the array is 1 MiB per GPU,
+ * held until exit); larger grids and runs with the entropy module are refused with PCB200_EARG /
+ * PCB200_EUNSUPP.  All calls share the array: calls that overlap on the GPU race. */
+#define PCB200_NOALLOC_MAX_BLOCKS 8192
+int pcb200_cfl_dt_noalloc(const double *f_dev, double *dt_out_dev);
+
 #ifdef __cplusplus
 }
 #endif

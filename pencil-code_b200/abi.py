@@ -109,6 +109,7 @@ SYMBOLS = {
     "pcb200_kernel_name": (C.c_char_p, []),
     "pcb200_last_error": (C.c_char_p, []),
     "pcb200_abi_version": (C.c_int, []),
+    "pcb200_cfl_dt_noalloc": (C.c_int, [C.c_void_p, C.c_void_p]),
 }
 
 

@@ -1263,3 +1263,76 @@ extern "C" int pcb200_timer_stop(float *ms)
 }
 extern "C" int pcb200_sync(void) { CK(cudaStreamSynchronize(g.st)); if (g.st_comm) CK(cudaStreamSynchronize(g.st_comm)); return PCB200_OK; }
 extern "C" int64_t pcb200_launch_count(void) { const int64_t n = g.launches; g.launches = 0; return n; }
+
+// ------------------------------------------------------------------------
+// pcb200_cfl_dt_noalloc: the CFL pre-pass (cfl_prepass -> fixed-order reduction -> dt) for callers that
+// must not allocate.  No counterpart in the reference.
+// The per-CTA partial maxima, which the regular path keeps in the cudaMalloc'ed g.partials, live in a
+// file-scope device array of NOALLOC_MAX_BLOCKS rows of NRED doubles (1 MiB, held by every GPU that loads the library
+// until exit).  Every call overwrites the entries it reads (one per CTA of its own launch), so nothing
+// has to start at zero; all calls share the array: calls that overlap on the GPU race.
+// ------------------------------------------------------------------------
+#define NOALLOC_MAX_BLOCKS PCB200_NOALLOC_MAX_BLOCKS   // 512^3 in 32x8x64 blocks
+#define NOALLOC_ZC 64
+static __device__ __align__(256) double noalloc_scratch[(size_t)NOALLOC_MAX_BLOCKS * NRED];
+
+// second pass: slot RD_DT1 of the nblocks rows in a fixed order, then finish_dt's formula (device code
+// may name the array directly; the host side below needs its address from cudaGetSymbolAddress)
+__global__ void noalloc_reduce_dt(const double *__restrict__ scratch, int nblocks, double dt1_floor, double *__restrict__ dt_out)
+{
+  __shared__ double sm[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double v = 0.0;
+  for (int b = threadIdx.x; b < nblocks; b += blockDim.x) v = fmax(v, scratch[(size_t)b * NRED + RD_DT1]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  if (lane == 0) sm[warp] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); w++) v = fmax(v, sm[w]);
+    const double d = fmax(v, dt1_floor);
+    dt_out[1] = d; dt_out[0] = 1.0 / d;
+  }
+}
+
+// device address of the scratch array, looked up once per device with that device current
+static int noalloc_scratch_ptr(double **out)
+{
+  static double *cache[64] = {nullptr};
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(PCB200_EARG, "pcb200_cfl_dt_noalloc: device ordinal out of range");
+  if (!cache[dev]) {
+    double *p = nullptr;
+    CK(cudaGetSymbolAddress((void **)&p, noalloc_scratch));
+    if (!p) return fail(PCB200_ECUDA, "cudaGetSymbolAddress(noalloc_scratch) returned a null address");
+    cache[dev] = p;
+  }
+  *out = cache[dev];
+  return PCB200_OK;
+}
+
+extern "C" int pcb200_cfl_dt_noalloc(const double *f_dev, double *dt_out_dev)
+{
+  if (!g.have_par) return fail(PCB200_ESTATE, "pcb200_cfl_dt_noalloc before pcb200_initialize");
+  if (!f_dev || !dt_out_dev) return fail(PCB200_EARG, "pcb200_cfl_dt_noalloc: null device pointer");
+  if (((uintptr_t)f_dev & 15) != 0 || ((uintptr_t)dt_out_dev & 7) != 0) return fail(PCB200_EARG, "pcb200_cfl_dt_noalloc: f_dev must be 16-byte aligned, dt_out_dev 8-byte aligned");
+  const pcb200_params &P = g.P;
+  if (P.lentropy) return fail(PCB200_EUNSUPP, "pcb200_cfl_dt_noalloc: the CFL pre-pass covers runs without the entropy module only");
+  dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (P.nz + NOALLOC_ZC - 1) / NOALLOC_ZC);
+  const long long nb = (long long)grd.x * grd.y * grd.z;
+  if (nb > NOALLOC_MAX_BLOCKS)
+    return fail(PCB200_EARG, "pcb200_cfl_dt_noalloc: grid needs " + std::to_string(nb) + " blocks of 32x8x64 cells, the static scratch holds " +
+                             std::to_string(NOALLOC_MAX_BLOCKS) + " (512^3 cells per rank)");
+  CK(cudaSetDevice(g.dev));
+  double *scratch = nullptr;
+  int rc = noalloc_scratch_ptr(&scratch);
+  if (rc) return rc;
+  if (P.lmagnetic) cfl_prepass<true><<<grd, blk, 0, g.st>>>(f_dev, scratch, 0, P.nz, NOALLOC_ZC);
+  else cfl_prepass<false><<<grd, blk, 0, g.st>>>(f_dev, scratch, 0, P.nz, NOALLOC_ZC);
+  const double floor1 = P.dtmax != 0.0 ? 1.0 / P.dtmax : 0.0;
+  noalloc_reduce_dt<<<1, 1024, 0, g.st>>>(scratch, (int)nb, floor1, dt_out_dev);
+  g.launches += 2;
+  CK(cudaGetLastError());
+  return PCB200_OK;
+}

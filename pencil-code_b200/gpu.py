@@ -135,6 +135,11 @@ class GPU:
         """fused RHS+RK kernel of the last substep launch (rhs_dly / rhs_tma / rhs_march / rhs_global)"""
         return self.lib.pcb200_kernel_name().decode()
 
+    def cfl_dt_noalloc(self, f_dev_ptr, dt_out_dev_ptr):
+        """pcb200_cfl_dt_noalloc: CFL dt of a device-resident f (ghosts valid) without any allocation; device
+        pointers as integers; asynchronous on the library's stream (sync() waits).  No reference counterpart."""
+        self._ck(self.lib.pcb200_cfl_dt_noalloc(C.c_void_p(int(f_dev_ptr)), C.c_void_p(int(dt_out_dev_ptr))))
+
     def enable_kernel_timing(self, on=True):
         self._ck(self.lib.pcb200_enable_kernel_timing(int(on)))
 
