@@ -15,6 +15,7 @@ struct DevPar {
   int mvar;
   int slot[NROLE];               // role -> storage slot, -1 = absent
   long long foff[NROLE];         // slot*mw: element offset of the role's variable
+  long long foff8[NROLE];        // the same in bytes
   int lupw_uu, lupw_lnrho, lupw_ss;
   int lbidiag;                 // lbidiagonal_derij (cdata.f90:568)
   int iheatcond, lcooling, lviscosity_heat, lohmic_heat, lgravz, ldensity, lhydro;

@@ -99,7 +99,7 @@ __global__ void reduce_partials(const double *__restrict__ partials, int nblocks
 // accessor over global memory
 // ------------------------------------------------------------------------
 struct GlobalAcc {
-  static constexpr bool PS = true;
+  static constexpr bool PS = true, UPW = true, NOZMIX = false;
   const double *p[NROLE];
   long long sy, sz;
   bool bd;
@@ -187,7 +187,7 @@ PC_DEV double lds_at(const double *base, unsigned byteoff, int imm_elems)
 
 template <bool MAG, bool ENT>
 struct MarchAcc {
-  static constexpr bool PS = true;
+  static constexpr bool PS = true, UPW = true, NOZMIX = false;
   const double *smem0;  // dynamic shared memory: ring [ring role][NSLOT][PE], then plain [plain role][2][PE]
   unsigned sb[7];       // byte offset of this thread's cell in the ring slot of plane z+k, k=-3..3
   unsigned pb;          // byte offset of this thread's cell in the plain-field slot of plane z
@@ -603,7 +603,9 @@ __device__ __forceinline__ bool mbar_test_wait(unsigned long long *bar, unsigned
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
 {
-  // bounded spin: a protocol error traps instead of hanging the GPU
+  // bounded spin: a protocol error traps instead of hanging the GPU (not unrolled: the copies of the
+  // poll made up a quarter of the z-loop body of rhs_dly, which has to stay in the instruction cache)
+#pragma unroll 1
   for (unsigned it = 0; it < (1u << 28); it++) if (mbar_try_wait(bar, parity)) return;
   __trap();
 }
@@ -617,6 +619,7 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, in
 
 template <bool MAG, bool ENT, bool BD = true>
 struct TmaAcc {
+  static constexpr bool UPW = true, NOZMIX = false;
   static constexpr bool PS = !(MAG && ENT);     // see physics.cuh: the 8-variable kernel spills more with the pre-scaled form
   PC_DEV constexpr bool bidiag() const { return BD; }
   const double *smem0;  // ring [ring role][NSLOT][PEP], then plain [plain role][2][PEP]
@@ -819,7 +822,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_tma(SubstepArgs a, const __grid_c
 // itself.  Same per-cell formula as hydro_pre/hydro_finish (AUX part); partials[block][RD_DT1].
 // ------------------------------------------------------------------------
 struct CflAcc {
-  static constexpr bool PS = true;
+  static constexpr bool PS = true, UPW = true, NOZMIX = false;
   const double *sm;     // [3 A fields][2 slots][PE]
   int cb;               // element offset of this thread's cell in the centre slot
   double wx[7], wy[7];  // own column of Ax, Ay, planes z-3..z+3

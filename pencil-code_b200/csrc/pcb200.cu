@@ -268,7 +268,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   if (P.lentropy) h.slot[R_SS] = P.iss - 1;
   if (P.lmagnetic) { h.slot[R_AX] = P.iax - 1; h.slot[R_AY] = P.iay - 1; h.slot[R_AZ] = P.iaz - 1; }
   for (int r = 0; r < NROLE; r++) if (h.slot[r] >= P.mvar) return fail(PCB200_EARG, "variable slot beyond mvar");
-  for (int r = 0; r < NROLE; r++) h.foff[r] = h.slot[r] >= 0 ? (long long)h.slot[r] * h.mw : 0;
+  for (int r = 0; r < NROLE; r++) { h.foff[r] = h.slot[r] >= 0 ? (long long)h.slot[r] * h.mw : 0; h.foff8[r] = h.foff[r] * 8; }
   h.lbidiag = P.lbidiagonal_derij;
   h.lupw_uu = P.lupw_uu; h.lupw_lnrho = P.lupw_lnrho; h.lupw_ss = P.lupw_ss;
   h.iheatcond = P.iheatcond; h.lcooling = P.lcooling; h.lviscosity_heat = P.lviscosity_heat; h.lohmic_heat = P.lohmic_heat;
@@ -355,10 +355,12 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
   OPTINT4(false, false); OPTINT4(true, false); OPTINT4(false, true); OPTINT4(true, true);
 #undef OPTINT4
 #undef OPTINT
-#define OPTIND(M, E) CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
-                     CK(cudaFuncSetAttribute(rhs_dly<M, E, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
-                     CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM))
+#define OPTIND1(M, E, U) CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, false, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
+                         CK(cudaFuncSetAttribute(rhs_dly<M, E, 1, false, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
+                         CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, true, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM))
+#define OPTIND(M, E) OPTIND1(M, E, false); OPTIND1(M, E, true)
   OPTIND(false, false); OPTIND(true, false); OPTIND(false, true);
+#undef OPTIND1
 #undef OPTIND
   CK(cudaStreamSynchronize(g.st));
   g.have_par = true;
@@ -586,12 +588,14 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
       *nblocks_out = grd.x * grd.y * grd.z;
       // centre-plane-only stencils, z-mixed terms finished three planes late from tensor memory
       constexpr int AX = AUXM < 2 ? AUXM : 0;
-      if (M) { if (rw) rhs_dly<true, false, 0, true><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
-               else    rhs_dly<true, false, AX, false><<<grd, blk, DlyCfg<true, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
-      else if (E) { if (rw) rhs_dly<false, true, 0, true><<<grd, blk, DlyCfg<false, true>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
-                    else    rhs_dly<false, true, AX, false><<<grd, blk, DlyCfg<false, true>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
-      else   { if (rw) rhs_dly<false, false, 0, true><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr);
-               else    rhs_dly<false, false, AX, false><<<grd, blk, DlyCfg<false, false>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); }
+      // upwinding is a compile-time property of the kernel (UPW), chosen from the run parameters
+      const bool upw = P.lupw_uu || P.lupw_lnrho || (E && P.lupw_ss);
+#define LD(MM, EE, UU) do { if (rw) rhs_dly<MM, EE, 0, true, UU><<<grd, blk, DlyCfg<MM, EE>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); \
+                            else    rhs_dly<MM, EE, AX, false, UU><<<grd, blk, DlyCfg<MM, EE>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); } while (0)
+      if (M)      { if (upw) LD(true, false, true);  else LD(true, false, false); }
+      else if (E) { if (upw) LD(false, true, true);  else LD(false, true, false); }
+      else        { if (upw) LD(false, false, true); else LD(false, false, false); }
+#undef LD
     } else {
     // the old 2N register is only read on substeps 2,3, which never need the reductions
 #define LT(M, E) do { if (P.lbidiagonal_derij) { \

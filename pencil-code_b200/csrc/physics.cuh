@@ -14,6 +14,30 @@
 
 #define PC_DEV __device__ __forceinline__
 
+// ---- exp for the density pencils ---------------------------------------
+// rho1 = exp(-lnrho) is evaluated in every cell.  The library routine materialises its eleven polynomial
+// coefficients as 22 immediates per call (measured in the z loop of rhs_dly: 60 instructions, 18 of them FP64);
+// here they are constant-bank operands of the FMAs.  Cody-Waite reduction x = n ln2 + r, |r| <= ln2/2, Taylor
+// polynomial of degree 13 (truncation 4e-18 relative), scaling by 2^n through the exponent field.  Arguments
+// beyond +-700 (never a physical ln rho; exp leaves the normal range at 709) saturate to inf / 0, NaN stays NaN.
+// No fallback call: a call inside the z loop cost 48 more shared-memory loads per cell (registers saved around it).
+__constant__ double c_expc[12] = {0.5, 0.16666666666666666, 0.041666666666666664, 0.008333333333333333, 0.001388888888888889, 0.0001984126984126984, 2.48015873015873e-05, 2.7557319223985893e-06, 2.755731922398589e-07, 2.505210838544172e-08, 2.08767569878681e-09, 1.6059043836821613e-10};   // 1/2! .. 1/13!
+PC_DEV double pc_exp(double x)
+{
+  const double t = fma(x, 1.4426950408889634, 6755399441055744.0);      // x*log2(e) + 1.5*2^52: n in the low word
+  const double tn = t - 6755399441055744.0;
+  double r = fma(tn, -6.93147180369123816490e-01, x);                  // ln2 high part (trailing zeros: n*hi is exact)
+  r = fma(tn, -1.90821492927058770002e-10, r);                         // ln2 low part
+  double q = c_expc[11];
+#pragma unroll
+  for (int k = 10; k >= 0; k--) q = fma(q, r, c_expc[k]);
+  q = fma(q, r, 1.0);
+  q = fma(q, r, 1.0);
+  const int n = __double2loint(t);
+  const double e = q * __hiloint2double((n + 1023) << 20, 0);
+  return fabs(x) < 700.0 ? e : (x != x ? x : (x > 0.0 ? __longlong_as_double(0x7ff0000000000000LL) : 0.0));
+}
+
 // ---- stencils ---------------------------------------------------------
 // Two formulations of the same stencils.  A::PS (pre-scaled): coefficients f*c_k come from the
 // constant bank (DevPar::k1x ...), one multiply-add per tap and merged Laplacian pairs: ~10 % fewer
@@ -85,6 +109,7 @@ template <int R, class A> PC_DEV double dxy(const A &a, const double *k, double 
 }
 template <int R, class A> PC_DEV double dxz(const A &a, const double *k, double fij)
 {
+  if (A::NOZMIX) return 0.0;
   if (!a.bidiag()) return PC_DFULL(xz);
   if (!A::PS)
     return fij * (270.0 * (a.template xz<R, 1, 1>() - a.template xz<R, -1, 1>() + a.template xz<R, -1, -1>() - a.template xz<R, 1, -1>())
@@ -96,6 +121,7 @@ template <int R, class A> PC_DEV double dxz(const A &a, const double *k, double 
 }
 template <int R, class A> PC_DEV double dyz(const A &a, const double *k, double fij)
 {
+  if (A::NOZMIX) return 0.0;
   if (!a.bidiag()) return PC_DFULL(yz);
   if (!A::PS)
     return fij * (270.0 * (a.template yz<R, 1, 1>() - a.template yz<R, -1, 1>() + a.template yz<R, -1, -1>() - a.template yz<R, 1, -1>())
@@ -140,9 +166,10 @@ PC_DEV void mag_part(const A &a, const DevPar &c, double ux, double uy, double u
   const double axxx = d2x<R_AX>(a, c), ax_yz = p2yz<R_AX>(a, c);
   const double ayyy = d2y<R_AY>(a, c), ay_zx = p2zx<R_AY>(a, c);
   const double azzz = d2z<R_AZ>(a, c), az_xy = p2xy<R_AZ>(a, c);
-  const double jx = c.mu01 * ((dxy<R_AY>(a, c.kxy, c.fxy) + dxz<R_AZ>(a, c.kzx, c.fzx)) - ax_yz);
-  const double jy = c.mu01 * ((dyz<R_AZ>(a, c.kyz, c.fyz) + dxy<R_AX>(a, c.kxy, c.fxy)) - ay_zx);
-  const double jz = c.mu01 * ((dxz<R_AX>(a, c.kzx, c.fzx) + dyz<R_AY>(a, c.kyz, c.fyz)) - az_xy);
+  // A::NOZMIX (rhs_dly): the z-mixed derivatives are completed three planes late, not here
+  const double jx = c.mu01 * (A::NOZMIX ? dxy<R_AY>(a, c.kxy, c.fxy) - ax_yz : (dxy<R_AY>(a, c.kxy, c.fxy) + dxz<R_AZ>(a, c.kzx, c.fzx)) - ax_yz);
+  const double jy = c.mu01 * (A::NOZMIX ? dxy<R_AX>(a, c.kxy, c.fxy) - ay_zx : (dyz<R_AZ>(a, c.kyz, c.fyz) + dxy<R_AX>(a, c.kxy, c.fxy)) - ay_zx);
+  const double jz = c.mu01 * (A::NOZMIX ? -az_xy : (dxz<R_AX>(a, c.kzx, c.fzx) + dyz<R_AY>(a, c.kyz, c.fyz)) - az_xy);
   m.bx = bx; m.by = by; m.bz = bz;
   m.j2 = jx * jx + jy * jy + jz * jz;
   m.fx = rho1 * (jy * bz - jz * by);
@@ -185,7 +212,7 @@ PC_DEV void hydro_pre(const A &a, const DevPar &c, int iz, double *__restrict__ 
   double uguy = ux * uyx + uy * uyy + uz * uyz;
   double uguz = ux * uzx + uy * uzy + uz * uzz;
   const double aux_ = fabs(ux), auy_ = fabs(uy), auz_ = fabs(uz);
-  if (c.lupw_uu) {
+  if (A::UPW && c.lupw_uu) {
     ugux -= aux_ * d6x<R_UX>(a, c.fx1) + auy_ * d6y<R_UX>(a, c.fy1) + auz_ * d6z<R_UX>(a, c.fz1);
     uguy -= aux_ * d6x<R_UY>(a, c.fx1) + auy_ * d6y<R_UY>(a, c.fy1) + auz_ * d6z<R_UY>(a, c.fz1);
     uguz -= aux_ * d6x<R_UZ>(a, c.fx1) + auy_ * d6y<R_UZ>(a, c.fy1) + auz_ * d6z<R_UZ>(a, c.fz1);
@@ -195,16 +222,16 @@ PC_DEV void hydro_pre(const A &a, const DevPar &c, int iz, double *__restrict__ 
   const double del2ux = uxxx + p2yz<R_UX>(a, c);
   const double del2uy = uyyy + p2zx<R_UY>(a, c);
   const double del2uz = uzzz + p2xy<R_UZ>(a, c);
-  const double gdx = uxxx + dxy<R_UY>(a, c.kxy, c.fxy) + dxz<R_UZ>(a, c.kzx, c.fzx);
-  const double gdy = dxy<R_UX>(a, c.kxy, c.fxy) + uyyy + dyz<R_UZ>(a, c.kyz, c.fyz);
-  const double gdz = dxz<R_UX>(a, c.kzx, c.fzx) + dyz<R_UY>(a, c.kyz, c.fyz) + uzzz;
+  const double gdx = A::NOZMIX ? uxxx + dxy<R_UY>(a, c.kxy, c.fxy) : uxxx + dxy<R_UY>(a, c.kxy, c.fxy) + dxz<R_UZ>(a, c.kzx, c.fzx);
+  const double gdy = A::NOZMIX ? dxy<R_UX>(a, c.kxy, c.fxy) + uyyy : dxy<R_UX>(a, c.kxy, c.fxy) + uyyy + dyz<R_UZ>(a, c.kyz, c.fyz);
+  const double gdz = A::NOZMIX ? uzzz : dxz<R_UX>(a, c.kzx, c.fzx) + dyz<R_UY>(a, c.kyz, c.fyz) + uzzz;
 
   // ---------------- density pencils (density.f90:2341) ----------------
   const double lnrho = a.template c<R_LNRHO>();
-  const double rho1 = exp(-lnrho);
+  const double rho1 = pc_exp(-lnrho);
   const double glx = ddx<R_LNRHO>(a, c), gly = ddy<R_LNRHO>(a, c), glz = ddz<R_LNRHO>(a, c);
   double uglnrho = ux * glx + uy * gly + uz * glz;
-  if (c.lupw_lnrho)
+  if (A::UPW && c.lupw_lnrho)
     uglnrho -= aux_ * d6x<R_LNRHO>(a, c.fx1) + auy_ * d6y<R_LNRHO>(a, c.fy1) + auz_ * d6z<R_LNRHO>(a, c.fz1);
   const double sglx = sxx * glx + sxy * gly + sxz * glz;
   const double sgly = sxy * glx + syy * gly + syz * glz;
@@ -230,7 +257,7 @@ PC_DEV void hydro_pre(const A &a, const DevPar &c, int iz, double *__restrict__ 
     gTx = c.gamma_m1 * glx + c.cv1 * gsx; gTy = c.gamma_m1 * gly + c.cv1 * gsy; gTz = c.gamma_m1 * glz + c.cv1 * gsz;
     del2lnTT = c.gamma_m1 * del2lnrho + c.cv1 * del2ss;
     ugss = ux * gsx + uy * gsy + uz * gsz;                         // entropy.f90:3189
-    if (c.lupw_ss)
+    if (A::UPW && c.lupw_ss)
       ugss -= aux_ * d6x<R_SS>(a, c.fx1) + auy_ * d6y<R_SS>(a, c.fy1) + auz_ * d6z<R_SS>(a, c.fz1);
     const double pf = -cs2 * c.gamma1;                             // entropy.f90:3209
     fpx = pf * (glx + gTx); fpy = pf * (gly + gTy); fpz = pf * (glz + gTz);
@@ -320,7 +347,7 @@ PC_DEV void rhs_cell(const A &a, const DevPar &c, int iz, double *__restrict__ r
   MagOut m;
   m.fx = m.fy = m.fz = m.j2 = m.advec_va2 = m.b2 = m.ab = m.jb = 0.0;
   if (MAG) {
-    const double rho1 = exp(-a.template c<R_LNRHO>());
+    const double rho1 = pc_exp(-a.template c<R_LNRHO>());
     mag_part<AUX>(a, c, a.template c<R_UX>(), a.template c<R_UY>(), a.template c<R_UZ>(), rho1, rhs + R_AX, m);
   }
   HydroPend p;

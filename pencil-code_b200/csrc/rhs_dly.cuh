@@ -90,9 +90,11 @@ template <bool MAG, bool ENT> struct DlyCfg {
 
 // centre-plane accessor: x/y neighbours from the ring slot of the centre plane, z from the
 // register window; the z-mixed accessors return 0 (those terms are completed in phase B)
-template <bool MAG, bool ENT>
+template <bool MAG, bool ENT, bool UPW_>
 struct DlyAcc {
-  static constexpr bool PS = true;
+  // UPW: upwinding compiled in (lupw_uu/lupw_lnrho/lupw_ss are run parameters; behind a run-time branch the
+  // compiler evaluated the 104 FP64 instructions of the der6 stencils in every cell, used or not)
+  static constexpr bool PS = true, UPW = UPW_, NOZMIX = true;
   PC_DEV constexpr bool bidiag() const { return true; }
   const double *smem0;
   unsigned cb;            // byte offset of this thread's cell in the ring slot of the centre plane
@@ -110,8 +112,8 @@ struct DlyAcc {
 };
 
 // the NC pre-scaled combinations of distance K on the centre plane
-template <bool MAG, bool ENT, int K>
-PC_DEV void dly_combos(const DlyAcc<MAG, ENT> &a, const DevPar &c, double *__restrict__ d)
+template <bool MAG, bool ENT, bool UPW, int K>
+PC_DEV void dly_combos(const DlyAcc<MAG, ENT, UPW> &a, const DevPar &c, double *__restrict__ d)
 {
   const double *su = c.dlyu[K - 1], *sa = c.dlya[K - 1];      // nu/3*c_K*{fzx,fyz}, mu01*c_K*{fzx,fyz}
   d[0] = su[0] * a.template dx<R_UZ, K>();                                           // nu/3 dxz(uz)
@@ -124,7 +126,7 @@ PC_DEV void dly_combos(const DlyAcc<MAG, ENT> &a, const DevPar &c, double *__res
   }
 }
 
-template <bool MAG, bool ENT, int AUXM, bool RW>
+template <bool MAG, bool ENT, int AUXM, bool RW, bool UPW>
 __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_constant__ CUtensorMap tmap,
                                                    const __grid_constant__ CUtensorMap tmap_wu, const __grid_constant__ CUtensorMap tmap_wr)
 {
@@ -206,7 +208,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
 #pragma unroll 1
     for (int g = 0; g < DLY_NGRP; g++) tm_st_group<NC>(t0, g, z6);
   }
-  DlyAcc<MAG, ENT> acc;
+  DlyAcc<MAG, ENT, UPW> acc;
   acc.smem0 = smem;
 #pragma unroll
   for (int r = 0; r < NROLE; r++)
@@ -216,6 +218,12 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
 #pragma unroll
   for (int q = 0; q < NRED; q++) red[q] = 0.0;
   const double beta_dt = a.write_f ? a.beta * a.dt_dev[0] : 0.0;
+  // store addresses as byte pointers: one pointer into w advanced by a plane per step, the role's offset
+  // added from the constant bank, f_out at a fixed distance from w (64-bit element indices scaled by 8 cost
+  // five integer instructions per store)
+  char *pw = reinterpret_cast<char *>(a.w) + ((long long)zb * c.sz + col) * 8;        // centre plane of step 0 is zb-NG (interior-relative)
+  const long long f_minus_w = reinterpret_cast<char *>(a.f_out) - reinterpret_cast<char *>(a.w);
+  const long long sz8 = c.sz * 8;
   mbar_wait(full, 0);
   // window of step 0: centre = ring plane 0, planes 0..3 are in the ring
 #pragma unroll
@@ -245,27 +253,26 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     }
     const bool doA = FULL || (s >= 3 && s < nzc + 3);   // phase A produces output (centre plane inside the chunk)
     const bool doB = FULL || s >= 6;                    // phase B finishes plane n-3
-    const long long idx = (long long)(n + NG) * c.sz + col;
-    const long long idxB = idx - 3 * c.sz;
+    char *const pwB = pw - 3 * sz8;
     // ---- phase A: everything of plane n except the z-mixed terms ----
     acc.cb = (unsigned)((c6 * Cfg::SLD + tb) * 8);
     // the pre-scaled x/y differences go to the history at once (slots that are not read in this step)
     {
       double d[6];
-      dly_combos<MAG, ENT, 1>(acc, c, d);
+      dly_combos<MAG, ENT, UPW, 1>(acc, c, d);
       tm_st_group<NC>(t0, c5, d);
-      dly_combos<MAG, ENT, 2>(acc, c, d);
+      dly_combos<MAG, ENT, UPW, 2>(acc, c, d);
       tm_st_group<NC>(t0, 5 + c6, d);
     }
     double d3[6];
-    dly_combos<MAG, ENT, 3>(acc, c, d3);
+    dly_combos<MAG, ENT, UPW, 3>(acc, c, d3);
     tm_st_group<NC>(t0, 11 + c7, d3);
     double rhs[NROLE];
     CellAux aux;
     MagOut m;
     m.fx = m.fy = m.fz = m.j2 = m.advec_va2 = m.b2 = m.ab = m.jb = 0.0;
     m.bx = m.by = m.bz = 0.0;
-    const double rho1 = exp(-acc.template c<R_LNRHO>());
+    const double rho1 = pc_exp(-acc.template c<R_LNRHO>());
     if (MAG) mag_part<(AUXM > 0)>(acc, c, acc.template c<R_UX>(), acc.template c<R_UY>(), acc.template c<R_UZ>(), rho1, rhs + R_AX, m);
     HydroPend hp;
     hydro_pre<MAG, ENT, (AUXM > 0)>(acc, c, FULL ? n : min(max(n, 0), c.nz - 1), rhs, aux, hp);
@@ -298,10 +305,10 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
 #pragma unroll
     for (int r = 3; r < NROLE; r++) {
       if (!role_present<MAG, ENT>(r)) continue;
-      const long long i = idx + c.foff[r];
+      char *const q = pw + c.foff8[r];
       const double wv = RW ? rhs[r] + a.alpha * wold[r] : rhs[r];
-      if (ww && doA) __stcs(a.w + i, wv);
-      if (wf && doA) __stcs(a.f_out + i, acc.w[r][3] + beta_dt * wv);
+      if (ww && doA) __stcs(reinterpret_cast<double *>(q), wv);
+      if (wf && doA) __stcs(reinterpret_cast<double *>(q + f_minus_w), acc.w[r][3] + beta_dt * wv);
     }
     if (AUXM > 0 && active && doA) red[RD_DT1] = fmax(red[RD_DT1], aux.dt1);
     tm_wait_ld();
@@ -325,14 +332,15 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     }
 #pragma unroll
     for (int r = 0; r < 3; r++) {
-      const long long i = idxB + c.foff[r];
+      char *const q = pwB + c.foff8[r];
       const double wv = RW ? ru[r] + a.alpha * wold[r] : ru[r];
-      if (ww && doB) __stcs(a.w + i, wv);
-      if (wf && doB) __stcs(a.f_out + i, acc.w[r][0] + beta_dt * wv);
+      if (ww && doB) __stcs(reinterpret_cast<double *>(q), wv);
+      if (wf && doB) __stcs(reinterpret_cast<double *>(q + f_minus_w), acc.w[r][0] + beta_dt * wv);
     }
 
     // ---- next plane: shift the z window, release the centre slot ----
     if (s + 1 == nstep) return;
+    pw += sz8;
     const bool have4 = s + 4 < nstep;
     if (have4) mbar_wait(full + (s & 1), (unsigned)((s >> 1) & 1));   // ring plane s+4: phase s/2 of full[s&1]
     const int nl = c6 >= 2 ? c6 - 2 : c6 + 4;                         // slot of ring plane s+4

@@ -19,7 +19,8 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpcb200.so")
+# PCB200_LIB: another build of the same library (A/B timing of kernel variants); the default is the in-tree build
+LIB_PATH = os.environ.get("PCB200_LIB") or os.path.join(_HERE, "libpcb200.so")
 
 
 class PCB200Error(RuntimeError):
