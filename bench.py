@@ -99,7 +99,10 @@ def timing_oracle(pk):
 def cpu_arm_setup(pk, args):
     """the GPU arm's physics on a bounded n^3 sample of its grid"""
     n = args.cpu_n
-    if args.hydro:
+    if args.convslab:
+        P, zprof, grid = pk.setups.config_convslab(n, n, n)
+        name = "conv-slab (hydro + entropy + gravity, walls in z)"
+    elif args.hydro:
         P, zprof, grid = pk.setups.config_hydro(n)
         name = "isothermal hydro"
     elif args.entropy:
@@ -109,6 +112,14 @@ def cpu_arm_setup(pk, args):
         P, zprof, grid = pk.setups.config_mhd(n)
         name = "isothermal MHD"
     return P, zprof, grid, name
+
+
+def bench_fields(pk, args, P, grid):
+    """deterministic synthetic fields; conv-slab: small density contrast so that the stratified walls stay tame"""
+    f = pk.setups.synthetic_fields(P, grid)
+    if args.convslab:
+        f[P.ilnrho - 1] *= 0.1
+    return f
 
 
 def run_reference(args):
@@ -122,7 +133,7 @@ def run_reference(args):
     n = args.cpu_n
     P, zprof, grid, name = cpu_arm_setup(pk, args)
     orc.set_zprofiles(zprof)
-    f = pk.setups.synthetic_fields(P, grid)
+    f = bench_fields(pk, args, P, grid)
     df = np.zeros_like(f)
     dt = 0.0
     for _ in range(args.warmup):
@@ -155,7 +166,7 @@ def cpu_baseline(pk, args, budget_s=15.0):
     n = args.cpu_n
     P, zprof, grid, name = cpu_arm_setup(pk, args)
     orc.set_zprofiles(zprof)
-    f = pk.setups.synthetic_fields(P, grid)
+    f = bench_fields(pk, args, P, grid)
     df = np.zeros_like(f)
     dt = orc.timestep(f, df, P, 0.0)
     t0 = time.perf_counter()
@@ -182,9 +193,11 @@ def parity_check(pk, dev, dist, rank, world, nproc, args, nsteps=3):
         kw.update(entropy=True, chi=1e-4, iheatcond=pk.abi.HCOND["chi-const"])
 
     def mk(npr, ipr):
+        if args.convslab:
+            return pk.setups.config_convslab(gx, gy, gz, nproc=npr, iproc=ipr)
         return pk.setups.make_params(gx, gy, gz, magnetic=not args.hydro, nproc=npr, iproc=ipr, **kw)
     P, zprof, grid = mk(nproc, rank)
-    f = pk.setups.synthetic_fields(P, grid)
+    f = bench_fields(pk, args, P, grid)
     dev.initialize_GPU(P, zprof)
     dev.register_GPU(f)
     dts = []
@@ -207,7 +220,7 @@ def parity_check(pk, dev, dist, rank, world, nproc, args, nsteps=3):
     if rank == 0:
         orc = entry.oracle()
         Pg, zpg, gg = mk((1, 1, 1), 0)
-        fo = pk.setups.synthetic_fields(Pg, gg)
+        fo = bench_fields(pk, args, Pg, gg)
         orc.set_zprofiles(zpg)
         dfo = np.zeros_like(fo)
         dto, d = [], 0.0
@@ -233,6 +246,8 @@ def parity_check(pk, dev, dist, rank, world, nproc, args, nsteps=3):
 
 
 def workload_name(args, n):
+    if args.convslab:
+        return f"samples/conv-slab physics (BASELINE config 1: hydro + entropy + gravity, K-profile, cooling, walls in z), {n}^3 cells per GPU, mvar=5"
     if args.hydro:
         return f"periodic isothermal hydro box (BASELINE config 2), {n}^3 cells per GPU, mvar=4"
     if args.entropy:
@@ -256,7 +271,10 @@ def main():
     ap.add_argument("--particles", type=int, default=0,
                     help="dust particles per GPU (BASELINE config 5 is 256^3 cells + 1.25e7 particles per GPU)")
     ap.add_argument("--entropy", action="store_true", help="BASELINE config 4 physics: MHD + entropy (chi-const), mvar=8")
+    ap.add_argument("--convslab", action="store_true", help="BASELINE config 1 physics: samples/conv-slab (use with --ncell 32 or 128; shipped resolution 32^3)")
     ap.add_argument("--decomp", default="", help="nprocx,nprocy,nprocz (default: z-slabs 1,1,N)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: n^3 cells per GPU (default, the driver's scaling run); strong: n^3 cells in total (SURVEY 8e table)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -286,13 +304,20 @@ def main():
     assert nproc[0] * nproc[1] * nproc[2] == world, "--decomp does not multiply to the world size"
     parity = None if args.no_parity_check else parity_check(pk, dev, dist, rank, world, nproc, args)
     n = args.n
-    # weak scaling: every GPU owns an n^3 slab, global box n x n x (n*world), dz kept equal
+    # weak scaling: every GPU owns an n^3 block, global box n*nprocx x n*nprocy x n*nprocz, grid spacing kept equal;
+    # strong scaling: the global box is n^3 and every GPU owns n/nprocx x n/nprocy x n/nprocz of it
     L = 2 * np.pi
+    strong = args.scaling == "strong"
+    gdim = (n, n, n) if strong else (n * nproc[0], n * nproc[1], n * nproc[2])
+    Lx = (L, L, L) if strong else (L * nproc[0], L * nproc[1], L * nproc[2])
     extra = dict(entropy=True, chi=1e-4, iheatcond=pk.abi.HCOND["chi-const"]) if args.entropy else {}
-    P, zprof, grid = pk.setups.make_params(n * nproc[0], n * nproc[1], n * nproc[2], magnetic=not args.hydro, nproc=nproc, iproc=rank,
-                                           Lxyz=(L * nproc[0], L * nproc[1], L * nproc[2]), nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3,
-                                           **extra)
-    f = pk.setups.synthetic_fields(P, grid)
+    if args.convslab:
+        P, zprof, grid = pk.setups.config_convslab(gdim[0], gdim[1], gdim[2], nproc=nproc, iproc=rank)
+    else:
+        P, zprof, grid = pk.setups.make_params(gdim[0], gdim[1], gdim[2], magnetic=not args.hydro, nproc=nproc, iproc=rank,
+                                               Lxyz=Lx, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3,
+                                               **extra)
+    f = bench_fields(pk, args, P, grid)
     dev.initialize_GPU(P, zprof)
     dev.register_GPU(f)
     dev.load_farray()
@@ -307,7 +332,7 @@ def main():
         if dist is not None:
             dist.barrier()
 
-    cells = n ** 3 * world
+    cells = gdim[0] * gdim[1] * gdim[2]
     fseq = pk.setups.forcing_sequence(args.steps + args.warmup) if args.forcing else None
     state = {"dt": 1e-3, "i": 0}
 
@@ -366,11 +391,13 @@ def main():
                "note": "registered host f uploaded once (rhs_GPU full=1), K steps, copy_farray_from_GPU once; "
                        "dt returned to the host every step"}
 
+    if os.environ.get("PCB200_TIME_GHOST"):
+        dev.finalize_GPU()        # prints the phase timers of this rank to stderr
     if rank != 0:
         return
     peak, peak_src = peaks()
     b_alg = B_ALG_PER_VAR * P.mvar
-    cells_local = n ** 3
+    cells_local = cells // world
     # kernel time per substep: at N>1 a substep is 3 launches (interior + 2 boundary slabs)
     ksub = kms * kcount / (3 * args.steps) if kcount else 0.0
     ach = cells_local * b_alg / (ksub * 1e-3) / 1e9 if ksub > 0 else None
@@ -384,17 +411,17 @@ def main():
     out = {
         "metric": "Mcell-updates/s per RK3 substep", "value": value, "unit": "Mcell-updates/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args, n),
-                   "global_grid": [n * nproc[0], n * nproc[1], n * nproc[2]], "decomposition": list(nproc), "step": "one RK3 time step = 3 substeps incl. BCs, CFL dt, 2N update",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args, n) if not strong else workload_name(args, n).replace("cells per GPU", "cells in total"),
+                   "global_grid": list(gdim), "decomposition": list(nproc), "step": "one RK3 time step = 3 substeps incl. BCs, CFL dt, 2N update",
                    "particles_per_gpu": args.particles, "forcing": bool(args.forcing), "l2": f"inputs larger than L2 ({f.nbytes / 1e9:.2f} GB per buffer)", "dt": dt},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if ach else None,
-                     "traffic": traffic, "peak_source": peak_src, "kernel": "%s<MAG=%d,ENT=%d>" % (dev.kernel_name(), int(not args.hydro), int(args.entropy)), "launches_timed": kcount,
+                     "traffic": traffic, "peak_source": peak_src, "kernel": "%s<MAG=%d,ENT=%d>" % (dev.kernel_name(), int(P.lmagnetic), int(P.lentropy)), "launches_timed": kcount,
                      "avg_launch_ms": kms, "kernel_ms_per_substep": ksub, "algorithmic_bytes_per_cell": b_alg,
                      "step_frac": cells_local * b_alg * 3 / (ms / args.steps * 1e-3) / 1e9 / peak,
                      # where the CFL pre-pass does not apply (entropy, PCB200_PREPASS=0) the f write of substep 1 is
                      # done by axpy_update, not by this kernel: its own share of the SURVEY 8d bytes is then 9/10
-                     "frac_kernel_own_bytes": ((0.9 if (args.entropy or os.environ.get("PCB200_PREPASS", "1") == "0") else 1.0)
+                     "frac_kernel_own_bytes": ((0.9 if (P.lentropy or os.environ.get("PCB200_PREPASS", "1") == "0") else 1.0)
                                                * ach / peak) if ach else None},
         "clocks": clk, "gpu_launches": launches, "parity_check": parity,
     }

@@ -512,6 +512,29 @@ __global__ void face_copy(FaceArgs a)
   double *q = a.buf + (long long)blockIdx.y * per_var + t;
   if (a.unpack == 0) *q = *p; else if (a.unpack == 1) *p = *q; else *p += *q;
 }
+// Both faces of one axis in one launch (x or y halo exchange): blockIdx.y = variable, threads over the lower
+// face first, then the upper one; 32-bit index arithmetic (a face has < 2^31 cells; the 64-bit divisions of
+// face_copy cost more than the copy).  Same buffer layouts as face_copy.  pack: lower/upper INTERIOR planes
+// (start NG and n) -> buf_lo/buf_hi; unpack: buf_lo -> lower ghosts (start 0), buf_hi -> upper ghosts (start NG+n).
+struct Face2Args { double *f; double *buf_lo; double *buf_hi; int axis, n, unpack, do_lo, do_hi; };
+__global__ void face_copy2(Face2Args a)
+{
+  const DevPar &c = c_par;
+  const unsigned mx = c.mx, my = c.my, mz = c.mz;
+  const unsigned per_var = a.axis == 0 ? NG * my * mz : NG * mx * mz;
+  unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 2 * per_var) return;
+  const bool hi = t >= per_var;
+  if (hi) t -= per_var;
+  if (hi ? !a.do_hi : !a.do_lo) return;
+  const unsigned start = a.unpack ? (hi ? NG + a.n : 0) : (hi ? a.n : NG);
+  unsigned ix, iy, iz;
+  if (a.axis == 0) { const unsigned r = t / NG; ix = start + (t - r * NG); iz = r / my; iy = r - iz * my; }
+  else { const unsigned r = t / mx; ix = t - r * mx; iz = r / NG; iy = start + (r - iz * NG); }
+  double *p = a.f + (long long)blockIdx.y * c.mw + (long long)iz * c.sz + (long long)iy * c.sy + ix;
+  double *q = (hi ? a.buf_hi : a.buf_lo) + (size_t)blockIdx.y * per_var + t;
+  if (a.unpack) *p = *q; else *q = *p;
+}
 // zero one plane (all blockIdx.y fields) -- the folded ghost layer (ghostfold_mpicomm.f90:69-70)
 __global__ void plane_zero(double *f, int axis, int plane)
 {

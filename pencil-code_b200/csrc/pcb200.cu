@@ -75,6 +75,7 @@ struct Ctx {
   bool zsplit = false;          // PCB200_ZSPLIT=1: interior planes overlap with the z halo exchange (3 launches per substep); default: wait for the halo, one launch -- faster since the kernels got shorter (28.4 vs 28.9 ms/step on 2 GPUs)
   bool use_prepass = true;      // isothermal runs: CFL pre-pass + fused update in substep 1 (PCB200_PREPASS=0: axpy pass)
   int zchunk_dly = 0;           // rhs_dly pays 6 extra steps per chunk: fewer, longer chunks
+  bool me_tma = false;          // PCB200_ME_TMA=1: magnetic+entropy on rhs_tma (the kernel of round 1) instead of rhs_dly
   int64_t launches = 0;
   float rhs_ms = 0.f; int rhs_n = 0; bool time_rhs = false;
   // multi-GPU
@@ -105,6 +106,21 @@ struct Ctx {
   std::string err;
 };
 static Ctx g;
+// PCB200_TIME_GHOST=1: CUDA events between the phases of the ghost-zone section of every substep (on the
+// stream the phase runs on); pcb200_finalize prints the average per phase
+static bool g_time_ghost = false;
+static std::vector<std::pair<int, cudaEvent_t>> g_ghost_ev;
+enum { GM_START = 0, GM_PACK, GM_NCCL, GM_UNPACK, GM_Z, GM_BC, GM_END,
+       // particle phases (same switch): around the gas kernel of a substep
+       PM_FIRST, PM_MIG_K, PM_MIG_X, PM_MAP, PM_CELLS, PM_DRAG, PM_GAS, PM_DEPOSIT, PM_FOLD, PM_BACK, GM_N };
+static const char *g_gm_name[GM_N] = {"start", "pack", "nccl x/y", "unpack", "z exchange", "bc/wrap", "wait",
+                                      "p:first+wrap", "p:migrate kernels", "p:migrate exchange+sync", "p:map+sort+gather", "p:cell bins",
+                                      "p:drag", "gas kernel etc", "p:deposit", "p:fold", "p:back-reaction"};
+static void ghost_mark(int tag, cudaStream_t st)
+{
+  if (!g_time_ghost) return;
+  cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); g_ghost_ev.push_back({tag, e});
+}
 
 static int fail(int code, const std::string &msg) { g.err = msg; return code; }
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
@@ -145,6 +161,7 @@ extern "C" int pcb200_init(int local_rank)
     g.use_global = k && !strcmp(k, "global");
     g.use_cpasync = k && !strcmp(k, "cpasync");
     g.use_dly = !k || !strcmp(k, "dly");
+    { const char *me = getenv("PCB200_ME_TMA"); g.me_tma = me && atoi(me) != 0; }
     const char *pp = getenv("PCB200_PREPASS");
     g.use_prepass = !pp || atoi(pp) != 0;
     const char *zs = getenv("PCB200_ZSPLIT");
@@ -152,6 +169,7 @@ extern "C" int pcb200_init(int local_rank)
     const char *ov = getenv("PCB200_OVERLAP_XY");
     g.overlap_force = ov ? (atoi(ov) != 0) : -1;
     g.bcs = g.st;
+    { const char *tg = getenv("PCB200_TIME_GHOST"); g_time_ghost = tg && atoi(tg) != 0; }
     const char *t = getenv("PCB200_TIME_RHS");
     g.time_rhs = t && atoi(t) != 0;
     g.inited = true;
@@ -225,7 +243,8 @@ static int make_tensor_maps()
       cuuint32_t box[4] = {HX, HY, 1, (cuuint32_t)h.mvar};
       CUtensorMap *tm = i < 2 ? &g.tmap4[i] : (i == 2 ? &g.tmap_wu : &g.tmap_wr);
       void *base = i < 2 ? (void *)g.f[i] : (void *)g.w;
-      if (i >= 2) { box[0] = TX + 2; box[1] = TY; box[3] = i == 2 ? 3 : (cuuint32_t)(h.mvar - 3); }
+      // w tiles: u (3 variables); the rest in one box, except magnetic+entropy: one-variable box (lnrho at plane n, ss at plane n-3)
+      if (i >= 2) { box[0] = TX + 2; box[1] = TY; box[3] = i == 2 ? 3 : ((P.lmagnetic && P.lentropy) ? 1 : (cuuint32_t)(h.mvar - 3)); }
       CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, base, dims, strides, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -339,7 +358,11 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
     const size_t nb_p = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * ((P.nz + 15) / 16);   // cfl_prepass
     const size_t nb_s = (size_t)((P.nx + TX - 1) / TX) * ((P.ny + TY - 1) / TY) * 70;                  // split launches, up to 64 chunks each
     const size_t need = std::max(std::max(std::max(nb_m, nb_g), nb_p), nb_s) * NRED;
-    if (need > g.npartials) { if (g.partials) cudaFree(g.partials); CK(cudaMalloc(&g.partials, need * sizeof(double))); g.npartials = need; }
+    if (need > g.npartials) {
+      if (g.partials) cudaFree(g.partials);
+      CK(cudaMalloc(&g.partials, need * sizeof(double))); g.npartials = need;
+      CK(cudaMemsetAsync(g.partials, 0, need * sizeof(double), g.st));     // dt-only steps write slot RD_DT1 only; reduce_partials reads all slots
+    }
   }
   CK(cudaMemcpyToSymbolAsync(c_par, &h, sizeof(DevPar), 0, cudaMemcpyHostToDevice, g.st));
   // opt in to the large dynamic shared memory of the marching kernels
@@ -359,7 +382,7 @@ extern "C" int pcb200_initialize(const pcb200_params *par)
                          CK(cudaFuncSetAttribute(rhs_dly<M, E, 1, false, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM)); \
                          CK(cudaFuncSetAttribute(rhs_dly<M, E, 0, true, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DlyCfg<M, E>::SMEM))
 #define OPTIND(M, E) OPTIND1(M, E, false); OPTIND1(M, E, true)
-  OPTIND(false, false); OPTIND(true, false); OPTIND(false, true);
+  OPTIND(false, false); OPTIND(true, false); OPTIND(false, true); OPTIND(true, true);
 #undef OPTIND1
 #undef OPTIND
   CK(cudaStreamSynchronize(g.st));
@@ -528,24 +551,27 @@ static int exchange_packed(double *f, int axis)
   const int n = axis == 0 ? P.nx : P.ny;
   const long long per_var = axis == 0 ? (long long)NG * h.my * h.mz : (long long)NG * h.mx * h.mz;
   const size_t cnt = (size_t)per_var * P.mvar;
-  dim3 blk(256), grd((unsigned)((per_var + 255) / 256), P.mvar);
-  auto copy = [&](double *buf, int start, int unpack) {
-    FaceArgs a; a.f = f; a.buf = buf; a.axis = axis; a.start = start; a.unpack = unpack; a.nplanes = NG;
-    face_copy<<<grd, blk, 0, g.bcs>>>(a);
-    g.launches++;
-  };
-  if (nlo >= 0) copy(g.face[0], NG, 0);          // lowest interior planes
-  if (nhi >= 0) copy(g.face[1], n, 0);           // highest interior planes
+  // both faces per launch: pack (lower/upper interior planes) -> one NCCL group -> unpack (upper/lower ghosts)
+  dim3 blk(256), grd((unsigned)((2 * per_var + 255) / 256), P.mvar);
+  Face2Args a; a.f = f; a.axis = axis; a.n = n; a.do_lo = nlo >= 0; a.do_hi = nhi >= 0;
+  ghost_mark(GM_BC, g.bcs);
+  a.buf_lo = g.face[0]; a.buf_hi = g.face[1]; a.unpack = 0;
+  face_copy2<<<grd, blk, 0, g.bcs>>>(a);
+  g.launches++;
   CK(cudaGetLastError());
+  ghost_mark(GM_PACK, g.bcs);
   NK(g.nccl.GroupStart());
   if (nlo >= 0) NK(g.nccl.Send(g.face[0], cnt, 8, nlo, g.comm, g.bcs));
   if (nhi >= 0) NK(g.nccl.Recv(g.face[3], cnt, 8, nhi, g.comm, g.bcs));
   if (nhi >= 0) NK(g.nccl.Send(g.face[1], cnt, 8, nhi, g.comm, g.bcs));
   if (nlo >= 0) NK(g.nccl.Recv(g.face[2], cnt, 8, nlo, g.comm, g.bcs));
   NK(g.nccl.GroupEnd());
-  if (nhi >= 0) copy(g.face[3], NG + n, 1);      // upper ghosts
-  if (nlo >= 0) copy(g.face[2], 0, 1);           // lower ghosts
+  ghost_mark(GM_NCCL, g.bcs);
+  a.buf_lo = g.face[2]; a.buf_hi = g.face[3]; a.unpack = 1;
+  face_copy2<<<grd, blk, 0, g.bcs>>>(a);
+  g.launches++;
   CK(cudaGetLastError());
+  ghost_mark(GM_UNPACK, g.bcs);
   return PCB200_OK;
 }
 
@@ -579,7 +605,7 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
     const CUtensorMap &tm = g.tmap[a.f_in == g.f[0] ? 0 : 1];
     const bool rw = a.alpha != 0.0;
     g.kname = "rhs_tma";
-    if (g.use_dly && g.have_dly && P.lbidiagonal_derij && AUXM < 2 && !(E && M)) {
+    if (g.use_dly && g.have_dly && P.lbidiagonal_derij && AUXM < 2 && !(E && M && g.me_tma)) {
       const CUtensorMap &tm4 = g.tmap4[a.f_in == g.f[0] ? 0 : 1];
       g.kname = "rhs_dly";
       a.zchunk = sub ? dly_chunk(a.ntx * a.nty, z_hi - z_lo) : g.zchunk_dly;
@@ -589,10 +615,12 @@ static int launch_rhs_t(const SubstepArgs &a0, int z_lo, int z_hi, size_t part_o
       // centre-plane-only stencils, z-mixed terms finished three planes late from tensor memory
       constexpr int AX = AUXM < 2 ? AUXM : 0;
       // upwinding is a compile-time property of the kernel (UPW), chosen from the run parameters
-      const bool upw = P.lupw_uu || P.lupw_lnrho || (E && P.lupw_ss);
+      // (the general variant also holds the isentropic eos of runs without the entropy module and gamma /= 1)
+      const bool upw = P.lupw_uu || P.lupw_lnrho || (E && P.lupw_ss) || (!E && P.gamma != 1.0);
 #define LD(MM, EE, UU) do { if (rw) rhs_dly<MM, EE, 0, true, UU><<<grd, blk, DlyCfg<MM, EE>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); \
                             else    rhs_dly<MM, EE, AX, false, UU><<<grd, blk, DlyCfg<MM, EE>::SMEM, g.st>>>(a, tm4, g.tmap_wu, g.tmap_wr); } while (0)
-      if (M)      { if (upw) LD(true, false, true);  else LD(true, false, false); }
+      if (M && E) { if (upw) LD(true, true, true);   else LD(true, true, false); }
+      else if (M) { if (upw) LD(true, false, true);  else LD(true, false, false); }
       else if (E) { if (upw) LD(false, true, true);  else LD(false, true, false); }
       else        { if (upw) LD(false, false, true); else LD(false, false, false); }
 #undef LD
@@ -840,6 +868,7 @@ static int part_migrate()
   part_mig_fill<<<nb, 256, 0, g.st>>>(q.npar, q.mpar, p.pre, p.counters, p.holes, p.tails, p.fp[p.cur], p.dfp[p.cur], p.ipar[p.cur]);
   g.launches += 5;
   CK(cudaGetLastError());
+  ghost_mark(PM_MIG_K, g.st);
   const size_t msg = (size_t)MIG_NVAL * mg.cap + 1;
   NK(g.nccl.GroupStart());
   for (int s = 0; s < mg.nslots; s++) {
@@ -858,6 +887,7 @@ static int part_migrate()
   if (err & 2) return fail(PCB200_EARG, "migrate_particles: too many particles migrating (raise PCB200_NPAR_MIG)");
   if (err & 4) return fail(PCB200_EARG, "migrate_particles: too many particles want to be at this rank (mpar_loc too small)");
   q.npar = p.counters_host[30];
+  ghost_mark(PM_MIG_X, g.st);
   return PCB200_OK;
 }
 
@@ -871,6 +901,7 @@ static int part_before_rhs(int isub)
   if (g.nranks > 1) {
     part_wrap<<<nb, 256, 0, g.st>>>(q, p.fp[p.cur]);
     g.launches++;
+    ghost_mark(PM_FIRST, g.st);
     int rcm = part_migrate();
     if (rcm) return rcm;
     nb = (unsigned)std::max(1, (q.npar + 255) / 256);
@@ -886,6 +917,7 @@ static int part_before_rhs(int isub)
   p.cur = nx;
   CK(cudaMemsetAsync(p.k1, 0, p.nimn * sizeof(int), g.st)); CK(cudaMemsetAsync(p.k2, 0, p.nimn * sizeof(int), g.st));
   part_pencil_bounds<<<nb, 256, 0, g.st>>>(q.npar, p.keys[1], p.k1, p.k2);
+  ghost_mark(PM_MAP, g.st);
   // cell bins for the gather-deposit: count per cell (= np), particles sorted by cell, bin offsets
   CK(cudaMemsetAsync(p.ccount, 0, ((size_t)p.ncell) * sizeof(int), g.st));
   part_cellkey<<<nb, 256, 0, g.st>>>(q.npar, q.mpar, p.inear[p.cur], p.ckeys[0], p.cvals[0], p.ccount);
@@ -899,6 +931,7 @@ static int part_before_rhs(int isub)
   // cs[ncell] = npar (npar changes when particles migrate)
   if (p.counters) CK(cudaMemcpyAsync(p.cs + p.ncell, p.counters + 30, sizeof(int), cudaMemcpyDeviceToDevice, g.st));
   CK(cub::DeviceScan::ExclusiveSum(p.cub_tmp, bytes, p.ccount, p.cs, p.ncell, g.st));
+  ghost_mark(PM_CELLS, g.st);
   (void)h;
   return PCB200_OK;
 }
@@ -959,6 +992,8 @@ static int part_fold_exchange(double *acc)
   return PCB200_OK;
 }
 
+// PCB200_TIME_GHOST=1: CUDA events around the ghost-zone section (boundary conditions, packed x/y faces,
+// z planes) of every substep on the compute stream; the sum is printed by pcb200_finalize
 static int do_substep(int isub, int ldiagnos)
 {
   const pcb200_params &P = g.P;
@@ -968,8 +1003,10 @@ static int do_substep(int isub, int ldiagnos)
   // boundcond.f90:1283-1290), each over the full extent of the other axes.  Per axis: wrap
   // locally / physical boundary condition / exchange with the neighbour ranks.  Consecutive
   // locally periodic axes share one launch.  Only the z exchange overlaps with compute.
+  ghost_mark(GM_START, g.st);
   if (g.part.on) if ((rc = part_before_rhs(isub))) return rc;
   const int np[3] = {P.nprocx, P.nprocy, P.nprocz};
+  if (g.part.on) ghost_mark(PM_CELLS, g.st);
   bool pend[3] = {false, false, false};
   auto flush = [&]() -> int {
     if (!pend[0] && !pend[1] && !pend[2]) return PCB200_OK;
@@ -982,7 +1019,8 @@ static int do_substep(int isub, int ldiagnos)
   const bool need_dt = first && P.ldt;
   // Isothermal runs: dt from a light CFL pre-pass over the start-of-step state, so that substep 1
   // applies the 2N update itself and the separate axpy pass over f and w disappears.
-  const bool prepass = need_dt && !ldiagnos && !P.lentropy && g.use_prepass;
+  // (isothermal = no entropy module and gamma = 1; with gamma /= 1 the sound speed varies from cell to cell)
+  const bool prepass = need_dt && !ldiagnos && !P.lentropy && P.gamma == 1.0 && g.use_prepass;
   // x/y-decomposed runs: the whole ghost-zone sequence (boundary conditions, packed x/y faces, z
   // planes) runs on the comm stream while the compute stream works on the tiles that need no ghost
   // cell; the boundary shell (first/last tile column and row, first/last NG planes) follows
@@ -1016,13 +1054,19 @@ static int do_substep(int isub, int ldiagnos)
       if ((rc = exchange_packed(fin, axis))) return rc;
     } else {
       if (!ovl) { CK(cudaEventRecord(g.ev_bc, g.st)); CK(cudaStreamWaitEvent(g.st_comm, g.ev_bc, 0)); }
+      ghost_mark(GM_BC, g.st);
       if ((rc = exchange_z(fin))) return rc;
+      ghost_mark(GM_Z, g.st_comm);
       if (!ovl) CK(cudaEventRecord(g.ev_halo, g.st_comm));
       if (lo || hi) if ((rc = launch_bc(fin, 2, lo, hi))) return rc;
     }
   }
   if ((rc = flush())) return rc;
   if (ovl) { CK(cudaEventRecord(g.ev_halo, g.st_comm)); g.bcs = g.st; }
+  if (g_time_ghost) {
+    ghost_mark(GM_BC, g.st);
+    if (multi && !ovl) { CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0)); ghost_mark(GM_END, g.st); }
+  }
   const int auxm = first ? (ldiagnos ? 2 : (need_dt ? 1 : 0)) : 0;
   SubstepArgs a; memset(&a, 0, sizeof(a));
   a.f_in = fin; a.w = g.w; a.f_out = fout;
@@ -1035,6 +1079,7 @@ static int do_substep(int isub, int ldiagnos)
   if (g.part.on) {
     if (multi) { CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0)); }
     if ((rc = part_pencils(fin, need_dt))) return rc;
+    ghost_mark(PM_DRAG, g.st);
   }
   int nb0 = 0, nb1 = 0, nb2 = 0;
   if (ovl) {
@@ -1061,7 +1106,7 @@ static int do_substep(int isub, int ldiagnos)
   } else if (prepass) {
     if (multi) CK(cudaStreamWaitEvent(g.st, g.ev_halo, 0));
     const char *zce = getenv("PCB200_PREPASS_ZC");
-    const int zc = zce && atoi(zce) > 0 ? atoi(zce) : 64;
+    const int zc = zce && atoi(zce) >= 16 ? atoi(zce) : 64;      // g.partials is sized for chunks of >= 16 planes
     dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (P.nz + zc - 1) / zc);
     if (P.lmagnetic) cfl_prepass<true><<<grd, blk, 0, g.st>>>(fin, g.partials, 0, P.nz, zc);
     else cfl_prepass<false><<<grd, blk, 0, g.st>>>(fin, g.partials, 0, P.nz, zc);
@@ -1095,18 +1140,23 @@ static int do_substep(int isub, int ldiagnos)
     // already produced the new state) f_out; otherwise axpy_update carries it (equ.f90:1046)
     Ctx::Part &pt = g.part;
     dim3 blk(128), grd((P.nx + 127) / 128, P.ny, P.nz);
+    ghost_mark(PM_GAS, g.st);
     if (g.nranks == 1) {
       part_deposit<false><<<grd, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta, nullptr);
       g.launches++;
+      ghost_mark(PM_DEPOSIT, g.st);
     } else {
       // split directions deposit into the first ghost layer, which fold_df ships to the neighbour
       CK(cudaMemsetAsync(pt.acc, 0, (size_t)4 * g.hp.mw * sizeof(double), g.st));
       dim3 grg((P.nx + 2 + 127) / 128, P.ny + 2, P.nz + 2);
       part_deposit<true><<<grg, blk, 0, g.st>>>(pt.q, fin, pt.drag, pt.cs, nullptr, nullptr, nullptr, g.dt_dev, 0.0, pt.acc);
       g.launches++;
+      ghost_mark(PM_DEPOSIT, g.st);
       if ((rc = part_fold_exchange(pt.acc))) return rc;
+      ghost_mark(PM_FOLD, g.st);
       part_backreact_acc<<<grd, blk, 0, g.st>>>(pt.q, fin, pt.acc, pt.rhop, g.w, a.write_f ? fout : nullptr, g.dt_dev, a.beta);
       g.launches++;
+      ghost_mark(PM_BACK, g.st);
     }
     CK(cudaGetLastError());
   }
@@ -1177,6 +1227,7 @@ extern "C" int pcb200_substep(int isubstep, int full, int early_finalize, int ld
   if (isubstep == 1 && !g.P.ldt) {
     // fixed time step: the caller's dt (or dt_fixed) is authoritative
     g.dt = (dt && *dt > 0.0) ? *dt : g.P.dt_fixed;
+    if (!(g.dt > 0.0)) return fail(PCB200_EARG, "pcb200_substep: ldt=0 needs a positive time step (*dt or dt_fixed)");
     g.pinned[0] = g.dt; g.pinned[1] = 1.0 / g.dt;
     CK(cudaMemcpyAsync(g.dt_dev, g.pinned, sizeof(double) * 2, cudaMemcpyHostToDevice, g.st));
     CK(cudaStreamSynchronize(g.st));
@@ -1245,6 +1296,20 @@ extern "C" int pcb200_finalize(void)
   if (!g.inited) return PCB200_OK;
   cudaSetDevice(g.dev);
   cudaStreamSynchronize(g.st);
+  if (g_time_ghost && !g_ghost_ev.empty()) {
+    double tot[GM_N] = {0}; size_t nsub = 0;
+    for (size_t i = 0; i < g_ghost_ev.size(); i++) {
+      if (g_ghost_ev[i].first == GM_START) { nsub++; continue; }
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, g_ghost_ev[i - 1].second, g_ghost_ev[i].second) == cudaSuccess) tot[g_ghost_ev[i].first] += ms;
+    }
+    fprintf(stderr, "[pcb200 rank %d] ghost-zone section, ms per substep over %zu substeps:", g.rank, nsub);
+    double all = 0.0;
+    for (int t = 1; t < GM_N; t++) { fprintf(stderr, " %s %.3f", g_gm_name[t], nsub ? tot[t] / nsub : 0.0); all += tot[t]; }
+    fprintf(stderr, " | total %.3f\n", nsub ? all / nsub : 0.0);
+    for (auto &e : g_ghost_ev) cudaEventDestroy(e.second);
+    g_ghost_ev.clear();
+  }
   free_fields();
   if (g.f_host_pinned) { cudaHostUnregister(g.f_host); g.f_host_pinned = false; }
   g.f_host = nullptr;
@@ -1322,7 +1387,7 @@ extern "C" int pcb200_cfl_dt_noalloc(const double *f_dev, double *dt_out_dev)
   if (!f_dev || !dt_out_dev) return fail(PCB200_EARG, "pcb200_cfl_dt_noalloc: null device pointer");
   if (((uintptr_t)f_dev & 15) != 0 || ((uintptr_t)dt_out_dev & 7) != 0) return fail(PCB200_EARG, "pcb200_cfl_dt_noalloc: f_dev must be 16-byte aligned, dt_out_dev 8-byte aligned");
   const pcb200_params &P = g.P;
-  if (P.lentropy) return fail(PCB200_EUNSUPP, "pcb200_cfl_dt_noalloc: the CFL pre-pass covers runs without the entropy module only");
+  if (P.lentropy || P.gamma != 1.0) return fail(PCB200_EUNSUPP, "pcb200_cfl_dt_noalloc: the CFL pre-pass covers isothermal runs only (no entropy module, gamma = 1)");
   dim3 blk(TX, TY), grd((P.nx + TX - 1) / TX, (P.ny + TY - 1) / TY, (P.nz + NOALLOC_ZC - 1) / NOALLOC_ZC);
   const long long nb = (long long)grd.x * grd.y * grd.z;
   if (nb > NOALLOC_MAX_BLOCKS)

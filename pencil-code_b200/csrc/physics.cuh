@@ -148,6 +148,7 @@ struct MagOut {
   double advec_va2;      // Alfven CFL term (magnetic.f90:5438)
   double b2, ab, jb;     // diagnostics
   double bx, by, bz;     // B itself (rhs_dly finishes the Lorentz force three planes late)
+  double jx, jy, jz;     // J (rhs_dly: its centre-plane part; Ohmic heating is finished three planes late)
 };
 
 // ---------------- magnetic (magnetic.f90:3587-3990, 4229-5589) ----------------
@@ -171,6 +172,7 @@ PC_DEV void mag_part(const A &a, const DevPar &c, double ux, double uy, double u
   const double jy = c.mu01 * (A::NOZMIX ? dxy<R_AX>(a, c.kxy, c.fxy) - ay_zx : (dyz<R_AZ>(a, c.kyz, c.fyz) + dxy<R_AX>(a, c.kxy, c.fxy)) - ay_zx);
   const double jz = c.mu01 * (A::NOZMIX ? -az_xy : (dxz<R_AX>(a, c.kzx, c.fzx) + dyz<R_AY>(a, c.kyz, c.fyz)) - az_xy);
   m.bx = bx; m.by = by; m.bz = bz;
+  m.jx = jx; m.jy = jy; m.jz = jz;
   m.j2 = jx * jx + jy * jy + jz * jz;
   m.fx = rho1 * (jy * bz - jz * by);
   m.fy = rho1 * (jz * bx - jx * bz);
@@ -262,7 +264,16 @@ PC_DEV void hydro_pre(const A &a, const DevPar &c, int iz, double *__restrict__ 
     const double pf = -cs2 * c.gamma1;                             // entropy.f90:3209
     fpx = pf * (glx + gTx); fpy = pf * (gly + gTy); fpz = pf * (glz + gTz);
   } else {
-    fpx = -cs2 * glx; fpy = -cs2 * gly; fpz = -cs2 * glz;          // noentropy.f90:291
+    // noentropy with gamma /= 1 selects the isentropic eos (noentropy.f90:113-116, leos_isentropic branch of
+    // calc_pencils_eos, eos_idealgas.f90:809-815): cs2 = cs20*exp(gamma_m1*(lnrho-lnrho0)), glnTT = gamma_m1*glnrho,
+    // fpres = -cs2*(glnrho+glnTT)/gamma.  Compiled in with A::UPW only (the general variant of rhs_dly).
+    if (A::UPW && c.gamma_m1 != 0.0) {
+      cs2 = c.cs20 * pc_exp(c.gamma_m1 * (lnrho - c.lnrho0));
+      const double pf = -cs2 * c.gamma1;
+      fpx = pf * (glx + c.gamma_m1 * glx); fpy = pf * (gly + c.gamma_m1 * gly); fpz = pf * (glz + c.gamma_m1 * glz);
+    } else {
+      fpx = -cs2 * glx; fpy = -cs2 * gly; fpz = -cs2 * glz;        // noentropy.f90:291
+    }
   }
 
   // ---------------- momentum (hydro.f90:3704, viscosity.f90:1421-1448,2571) ----------------
@@ -323,12 +334,13 @@ PC_DEV void hydro_pre(const A &a, const DevPar &c, int iz, double *__restrict__ 
 }
 
 // adds what depends on the induction part: Lorentz force, Ohmic heating, Alfven CFL term
-template <bool MAG, bool ENT, bool AUX>
+// OHM: Ohmic heating added here (rhs_dly adds it once the whole J is known)
+template <bool MAG, bool ENT, bool AUX, bool OHM = true>
 PC_DEV void hydro_finish(const DevPar &c, const HydroPend &p, const MagOut &m, double *__restrict__ rhs, CellAux &aux)
 {
   if (MAG) {
     rhs[R_UX] += m.fx; rhs[R_UY] += m.fy; rhs[R_UZ] += m.fz;
-    if (ENT) rhs[R_SS] += p.ohm * m.j2;
+    if (ENT && OHM) rhs[R_SS] += p.ohm * m.j2;
   }
   if (AUX) {
     const double maxadvec = p.advec_uu + sqrt((MAG ? m.advec_va2 : 0.0) + p.advec_cs2);

@@ -154,6 +154,7 @@ module GPU
 !
   logical, save :: lvery_first=.true.
   real(c_double), dimension(16), save :: gpu_diag
+  real, dimension(:,:,:,:), pointer, save :: f_registered => null()   ! the array handed over by register_GPU
 !
 contains
 !***********************************************************************
@@ -228,21 +229,58 @@ contains
 !  Refuse module combinations the kernels do not cover (same policy as
 !  gpu_astaroth.f90:32-71, shorter list: entropy and gravity ARE covered).
 !
-      use EquationOfState, only: cs20, gamma, lnrho0, get_cp1
-      use Hydro, only: Omega, lupw_uu
+!  Only names the reference exports are imported (eos.h:5,50,54, hydro.h:30, density.h:24, gravity.h:18-20);
+!  Omega, alpha_ts, beta_ts, mu0, cdt ... come from Cdata.  Module-private run parameters arrive through
+!  the reference's own route, pushpars2c (viscosity.f90:2951, magnetic.f90:10646, entropy.f90:8235), which
+!  hands out addresses; fortran/host.patch adds the Energy and Magnetic entries the device needs and turns
+!  the integer placeholders of noentropy.f90/nomagnetic.f90 into empty routines.
+!
+      use EquationOfState, only: cs20, gamma, lnrho0, get_cp1, cs2top
+      use Hydro, only: lupw_uu
       use Density, only: lupw_lnrho
-      use Viscosity, only: nu
-      use Magnetic, only: eta, lohmic_heat
-      use Energy, only: lupw_ss, lviscosity_heat, chi, hcond0, hcond1, hcond2, widthss, &
-                        cool, wcool, cs2cool, Fbot, iheatcond, hcond_prof, dlnhcond_prof
-      use Gravity, only: gravz, z1, z2
-      use Timestep, only: alpha_ts, beta_ts
+      use Viscosity, only: viscosity_pars => pushpars2c
+      use Magnetic, only: magnetic_pars => pushpars2c
+      use Energy, only: energy_pars => pushpars2c
+      use Gravity, only: gravz, z1, z2, gravz_profile
 !
       type(pcb200_params) :: par
       character(LEN=512) :: str
       real :: cp1
       real(c_double), dimension(nz) :: prof
       integer :: j, k
+      integer(KIND=ikind8), dimension(3)  :: p_visc      ! nu, zeta, idiag_dtnu
+      integer(KIND=ikind8), dimension(6)  :: p_mag       ! eta, lohmic_heat, idiag_jrms, idiag_jmax, idiag_abm, idiag_jbm
+      integer(KIND=ikind8), dimension(18) :: p_ene       ! see fortran/host.patch
+      real :: nu, eta, chi, hcond0, hcond1, hcond2, widthss, cool, wcool, cs2cool, Fbot
+      logical :: lohmic_heat, lupw_ss, lviscosity_heat, lheatc_Kprof, lheatc_chiconst
+      real, dimension(:), pointer :: hcond_prof, dlnhcond_prof
+!
+!  RELOAD (run.f90:571) while the device owns the state: bring f and the particles back before the device
+!  buffers are re-created, so that the upload that follows (lvery_first) starts from the current state
+!
+      if (.not.lvery_first .and. associated(f_registered)) then
+        call check(pcb200_copy_farray(f_registered),'initialize_GPU')
+        if (lparticles) call copy_particles_from_GPU(f_registered)
+      endif
+!
+      nu=0.; eta=0.; chi=0.; hcond0=0.; hcond1=0.; hcond2=0.; widthss=0.; cool=0.; wcool=1.; cs2cool=0.; Fbot=0.
+      lohmic_heat=.false.; lupw_ss=.false.; lviscosity_heat=.false.; lheatc_Kprof=.false.; lheatc_chiconst=.false.
+      nullify(hcond_prof); nullify(dlnhcond_prof)
+      call viscosity_pars(p_visc); nu=real_at(p_visc(1))
+      if (lmagnetic) then
+        call magnetic_pars(p_mag); eta=real_at(p_mag(1)); lohmic_heat=logical_at(p_mag(2))
+      endif
+      if (lentropy) then
+        call energy_pars(p_ene)
+        chi=real_at(p_ene(1)); hcond0=real_at(p_ene(2)); hcond1=real_at(p_ene(3)); hcond2=real_at(p_ene(4))
+        widthss=real_at(p_ene(5)); cool=real_at(p_ene(6)); wcool=real_at(p_ene(7)); cs2cool=real_at(p_ene(8))
+        Fbot=real_at(p_ene(9)); lupw_ss=logical_at(p_ene(10)); lviscosity_heat=logical_at(p_ene(11))
+        lheatc_Kprof=logical_at(p_ene(12)); lheatc_chiconst=logical_at(p_ene(13))
+        if (p_ene(14)/=0) then
+          call c_f_pointer(transfer(p_ene(14),c_null_ptr),hcond_prof,(/nz/))
+          call c_f_pointer(transfer(p_ene(15),c_null_ptr),dlnhcond_prof,(/nz/))
+        endif
+      endif
 !
       str=''
       if (lanelastic) str=trim(str)//', '//'anelastic'
@@ -280,6 +318,11 @@ contains
       if (.not.lcartesian_coords) str=trim(str)//', '//'curvilinear coordinates'
       if (.not.all(lequidist)) str=trim(str)//', '//'non-equidistant grid'
       if (itorder/=3) str=trim(str)//', '//'itorder/=3'
+      if (lgravz .and. gravz_profile/='const') str=trim(str)//', '//'gravz_profile/=const'
+      if (lgravx .or. lgravy) str=trim(str)//', '//'gravity along x or y'
+!  Not visible from here (module-private, not handed out by pushpars2c): ivisc, iresistivity, lweyl_gauge,
+!  hydro's theta.  The device implements ivisc='nu-const', iresistivity='eta-const', the Weyl gauge and
+!  theta=0 (the defaults of the samples this path covers); INTEGRATION.md lists them.
       if (str/='') call fatal_error('initialize_GPU','No GPU implementation for "'//trim(str(3:))//'"')
 !
       par%abi_version=PCB200_ABI_VERSION
@@ -295,12 +338,10 @@ contains
       par%lgravz=merge(1,0,lgravz); par%lforcing=merge(1,0,lforcing)
       par%lupw_uu=merge(1,0,lupw_uu); par%lupw_lnrho=merge(1,0,lupw_lnrho); par%lupw_ss=merge(1,0,lupw_ss)
       par%lbidiagonal_derij=merge(1,0,lbidiagonal_derij)
-      select case (iheatcond(1))
-      case ('nothing');   par%iheatcond=0
-      case ('K-profile'); par%iheatcond=1
-      case ('chi-const'); par%iheatcond=2
-      case default; call fatal_error('initialize_GPU','No GPU implementation for iheatcond='//trim(iheatcond(1)))
-      endselect
+      par%iheatcond=0
+      if (lheatc_Kprof) par%iheatcond=1
+      if (lheatc_chiconst) par%iheatcond=2
+      if (lheatc_Kprof.and.lheatc_chiconst) call fatal_error('initialize_GPU','No GPU implementation for two iheatcond at once')
       par%lcooling=merge(1,0,cool/=0.)
       par%lviscosity_heat=merge(1,0,lviscosity_heat)
       par%lohmic_heat=merge(1,0,lohmic_heat)
@@ -379,9 +420,10 @@ contains
 !
 !  run.f90:223 -- hand over the address of f once (aliased, never freed).
 !
-      real, dimension(:,:,:,:), intent(IN) :: f
+      real, dimension(:,:,:,:), intent(IN), target :: f
 !
       call check(pcb200_register(f),'register_GPU')
+      f_registered => f
 !
     endsubroutine register_GPU
 !***********************************************************************
@@ -399,7 +441,7 @@ contains
 !  cdata:dt and t (timestep.f90:152-190) stay right.
 !
       use Forcing, only: forcing_pars_hel
-      use Particles_cdata, only: fp, ipar
+      use Particles_cdata, only: fp, ipar, npar_loc
 !
       real, dimension (mx,my,mz,mfarray), intent(INOUT) :: f
       integer,                            intent(IN)    :: isubstep
@@ -410,12 +452,6 @@ contains
       real :: phase, fact
       real(c_double) :: dtc
 !
-      if (lforcing .and. isubstep==1) then
-!  coefficients of this step's delta-correlated kick (random numbers stay on the host)
-        call forcing_pars_hel(coef1,coef2,coef3,fda,kk,phase,fact)
-        frc%coef1=coef1; frc%coef2=coef2; frc%fda=fda; frc%kk=kk; frc%phase=phase; frc%fact=fact
-        call check(pcb200_set_forcing(frc),'rhs_GPU')
-      endif
 !  particles travel with f: uploaded once, then owned by the device
 !  (the host skips particles_timestep_first/second and particles_boundconds when lgpu)
       if (lparticles .and. lvery_first) call check(pcb200_particles_load(fp,ipar),'rhs_GPU')
@@ -423,6 +459,15 @@ contains
       call check(pcb200_substep(int(isubstep,c_int),merge(1_c_int,0_c_int,lvery_first), &
                                 merge(1_c_int,0_c_int,early_finalize),merge(1_c_int,0_c_int,ldiagnos),dtc),'rhs_GPU')
       if (isubstep==1 .and. ldt) dt=dtc
+      if (lforcing .and. isubstep==1) then
+!  Coefficients of this step's delta-correlated kick (the random numbers stay on the host; one draw per
+!  step).  Drawn AFTER substep 1 has returned the new dt: fact=force/ffnorm*sqrt(dt) (forcing.f90:1741),
+!  and the reference calls addforce after time_step (run.f90:683,729), i.e. with the dt of this step.
+!  The device applies the kick after substep 3.
+        call forcing_pars_hel(coef1,coef2,coef3,fda,kk,phase,fact)
+        frc%coef1=coef1; frc%coef2=coef2; frc%fda=fda; frc%kk=kk; frc%phase=phase; frc%fact=fact
+        call check(pcb200_set_forcing(frc),'rhs_GPU')
+      endif
       if (isubstep==1 .and. ldiagnos) then
         call check(pcb200_get_diagnostics(gpu_diag,16_c_int),'rhs_GPU')
         call diagnostics_to_fname
@@ -464,40 +509,85 @@ contains
 !***********************************************************************
     subroutine diagnostics_to_fname
 !
-!  0-D diagnostics computed on the device go straight into fname, so that
-!  print.in/time_series.dat work without the full D2H copy of equ.f90:344-347.
-!  The indices idiag_* are module-private; Hydro and Magnetic hand out their
-!  addresses through pushdiags2c (hydro.f90:8110, magnetic.f90:10657), which
-!  also sets the reduction type (sum->sqrt, max).  gpu_diag follows the
-!  PCB200_DIAG_* order of pcb200.h.
+!  The 0-D diagnostics computed on the device (16 sums and maxima of substep 1, PCB200_DIAG_* order of
+!  pcb200.h) go straight into fname, so that print.in/time_series.dat work without the full D2H copy and
+!  the host pass of equ.f90:344-347 (fortran/host.patch takes ldiagnos out of that branch; 1-D/2-D averages
+!  still use it).  fname gets the raw sum or maximum and itype_name the finishing rule of diagnostic()
+!  (diagnostics.f90:643-716), exactly what sum_mn_name/max_mn_name leave behind.  The idiag_* indices are
+!  module-private: Hydro, Density and Magnetic hand out addresses through pushdiags2c (hydro.f90:8110,
+!  density.f90:4016, magnetic.f90:10657); host.patch appends idiag_oum, idiag_dtu (Hydro), idiag_jrms,
+!  idiag_jmax, idiag_abm, idiag_jbm (Magnetic), idiag_ssm, idiag_dtc, idiag_dtchi (Energy) and idiag_dtnu
+!  (Viscosity) to the same tables.
 !
       use Hydro, only: hydro_diags => pushdiags2c
-      use Magnetic, only: magnetic_diags => pushdiags2c
+      use Density, only: density_diags => pushdiags2c
+      use Magnetic, only: magnetic_diags => pushdiags2c, magnetic_pars => pushpars2c
+      use Energy, only: energy_pars => pushpars2c
+      use Viscosity, only: viscosity_pars => pushpars2c
 !
-      integer(KIND=ikind8), dimension(12) :: p_hyd
-      integer(KIND=ikind8), dimension(8) :: p_mag
+      integer(KIND=ikind8), dimension(14) :: p_hyd
+      integer(KIND=ikind8), dimension(5)  :: p_den
+      integer(KIND=ikind8), dimension(8)  :: p_mag
+      integer(KIND=ikind8), dimension(6)  :: p_magp
+      integer(KIND=ikind8), dimension(18) :: p_ene
+      integer(KIND=ikind8), dimension(3)  :: p_visc
 !
-      if (lhydro) then
-        call hydro_diags(p_hyd)
-        call put(p_hyd(1),gpu_diag(1))              ! idiag_urms: sum of u^2 (ilabel_sum_sqrt)
-        call put(p_hyd(5),sqrt(gpu_diag(2)))        ! idiag_umax (ilabel_max)
-      endif
+      call hydro_diags(p_hyd)
+      call put(p_hyd(1),gpu_diag(1),ilabel_sum_sqrt)        ! urms: sum u^2
+      call put(p_hyd(5),gpu_diag(2),ilabel_max_sqrt)        ! umax: max u^2
+      call put(p_hyd(13),gpu_diag(16),ilabel_sum)           ! oum
+      call put(p_hyd(14),gpu_diag(10),ilabel_max_dt)        ! dtu: max advec_uu/cdt
+      call density_diags(p_den)
+      call put(p_den(1),gpu_diag(3),ilabel_sum)             ! rhom
+      call viscosity_pars(p_visc)
+      call put(p_visc(3),gpu_diag(11),ilabel_max_dt)        ! dtnu
       if (lmagnetic) then
         call magnetic_diags(p_mag)
-        call put(p_mag(1),gpu_diag(5))              ! idiag_brms: sum of b^2
-        call put(p_mag(2),sqrt(gpu_diag(6)))        ! idiag_bmax
+        call put(p_mag(1),gpu_diag(5),ilabel_sum_sqrt)      ! brms: sum b^2
+        call put(p_mag(2),gpu_diag(6),ilabel_max_sqrt)      ! bmax: max b^2
+        call magnetic_pars(p_magp)
+        call put(p_magp(3),gpu_diag(7),ilabel_sum_sqrt)     ! jrms
+        call put(p_magp(4),gpu_diag(8),ilabel_max_sqrt)     ! jmax
+        call put(p_magp(5),gpu_diag(14),ilabel_sum)         ! abm
+        call put(p_magp(6),gpu_diag(15),ilabel_sum)         ! jbm
+      endif
+      if (lentropy) then
+        call energy_pars(p_ene)
+        call put(p_ene(16),gpu_diag(4),ilabel_sum)          ! ssm
+        call put(p_ene(17),gpu_diag(9),ilabel_max_dt)       ! dtc
+        call put(p_ene(18),gpu_diag(12),ilabel_max_dt)      ! dtchi
       endif
 !
     contains
-      subroutine put(addr,val)
+      subroutine put(addr,val,itype)
         integer(KIND=ikind8), intent(in) :: addr
         real(c_double), intent(in) :: val
-        type(c_ptr) :: cp
+        integer, intent(in) :: itype
         integer, pointer :: idiag
-        cp=transfer(addr,cp)
-        call c_f_pointer(cp,idiag)
-        if (idiag/=0) fname(idiag)=val
+        if (addr==0) return
+        call c_f_pointer(transfer(addr,c_null_ptr),idiag)
+        if (idiag/=0) then
+          fname(idiag)=val
+          itype_name(idiag)=itype
+        endif
       endsubroutine put
     endsubroutine diagnostics_to_fname
+!***********************************************************************
+    real function real_at(addr)
+!
+!  value of the real module variable whose address pushpars2c handed out (copy_addr, syscalls)
+!
+      integer(KIND=ikind8), intent(in) :: addr
+      real, pointer :: p
+      call c_f_pointer(transfer(addr,c_null_ptr),p)
+      real_at=p
+    endfunction real_at
+!***********************************************************************
+    logical function logical_at(addr)
+      integer(KIND=ikind8), intent(in) :: addr
+      logical, pointer :: p
+      call c_f_pointer(transfer(addr,c_null_ptr),p)
+      logical_at=p
+    endfunction logical_at
 !***********************************************************************
 endmodule GPU

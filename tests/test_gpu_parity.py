@@ -64,6 +64,10 @@ CASES = {
     # lbidiagonal_derij=F, as samples/gputest/run.in sets: 36-point product derij (deriv.f90:1430-1557)
     "mhd_derij36": lambda pk: pk.setups.config_mhd(32, lbidiagonal_derij=0),
     "mhd_entropy_derij36": lambda pk: pk.setups.config_mhd_entropy(32, lbidiagonal_derij=0),
+    # noentropy with gamma /= 1: the isentropic eos (noentropy.f90:113-116, eos_idealgas.f90:809-815); 5/3 is the eos default
+    "hydro_isentropic": lambda pk: pk.setups.config_hydro(32, gamma=5.0 / 3.0),
+    "mhd_isentropic_upwind": lambda pk: pk.setups.config_mhd(32, gamma=5.0 / 3.0, lupw_lnrho=1),
+    "mhd_entropy_upwind": lambda pk: pk.setups.config_mhd_entropy(32, lupw_ss=1, lupw_uu=1),
 }
 
 
