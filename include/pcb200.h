@@ -177,6 +177,18 @@ int pcb200_timestep(int full, int ldiagnos, double *dt);
  * array). */
 int pcb200_copy_farray(double *f_host);
 
+/* wsnap + output_snap (snapshot.f90:286-302, io_dist.f90:110-167) from the device, without stalling the time loop.
+ * The reference copies all of f to the host synchronously (copy_farray_from_GPU, snapshot.f90:286) and then writes
+ * record 1 = f(mx,my,mz,mvar) incl. ghost zones, record 2 = t,x(mx),y(my),z(mz),dx,dy,dz.  pcb200_snapshot_begin
+ * costs the caller one device-to-device copy of f into a staging array; a worker thread then pulls it through two
+ * page-locked chunk buffers (PCB200_SNAP_CHUNK_MB, default 64) on its own stream and writes `path` in exactly that
+ * layout (Fortran sequential unformatted, 4-byte markers, gfortran subrecords above 2147483639 bytes), while the
+ * caller goes on with pcb200_substep.  One snapshot in flight: the next begin, pcb200_snapshot_wait and
+ * pcb200_finalize wait for it.  x,y,z: this rank's mesh incl. ghost points (cdata x,y,z). */
+int pcb200_snapshot_begin(const char *path, double t, const double *x, const double *y, const double *z,
+                          double dx, double dy, double dz);
+int pcb200_snapshot_wait(void);
+
 /* upload f from the host (NULL = registered array) -- `full` path stand-alone */
 int pcb200_load_farray(const double *f_host);
 

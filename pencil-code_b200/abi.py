@@ -110,6 +110,8 @@ SYMBOLS = {
     "pcb200_last_error": (C.c_char_p, []),
     "pcb200_abi_version": (C.c_int, []),
     "pcb200_cfl_dt_noalloc": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "pcb200_snapshot_begin": (C.c_int, [C.c_char_p, _d, C.c_void_p, C.c_void_p, C.c_void_p, _d, _d, _d]),
+    "pcb200_snapshot_wait": (C.c_int, []),
 }
 
 

@@ -141,6 +141,16 @@ class GPU:
         pointers as integers; asynchronous on the library's stream (sync() waits).  No reference counterpart."""
         self._ck(self.lib.pcb200_cfl_dt_noalloc(C.c_void_p(int(f_dev_ptr)), C.c_void_p(int(dt_out_dev_ptr))))
 
+    def snapshot_begin(self, path, t, grid):
+        """wsnap from the device (snapshot.f90:286-302 + io_dist.f90:110-167): returns at once, the file is written by
+        a worker thread while the time loop goes on; grid = dict(x, y, z incl. ghost points, dx, dy, dz)"""
+        x, y, z = (np.ascontiguousarray(grid[k], dtype=np.float64) for k in ("x", "y", "z"))
+        self._ck(self.lib.pcb200_snapshot_begin(str(path).encode(), float(t), x.ctypes.data, y.ctypes.data, z.ctypes.data,
+                                                float(grid["dx"]), float(grid["dy"]), float(grid["dz"])))
+
+    def snapshot_wait(self):
+        self._ck(self.lib.pcb200_snapshot_wait())
+
     def enable_kernel_timing(self, on=True):
         self._ck(self.lib.pcb200_enable_kernel_timing(int(on)))
 
