@@ -163,7 +163,8 @@ int pcb200_register(double *f_host);
  * RHS, CFL dt on substep 1, 2N-RK3 update) fully on the device.
  * isubstep in {1,2,3}; full!=0 uploads the registered host f first
  * (lvery_first, gpu_astaroth.f90:107,124); early_finalize is accepted for
- * interface parity (the device always completes halos itself).
+ * interface parity and IGNORED (the device always completes its halos itself).
+ * With ldt=0, *dt (or dt_fixed) must be positive: PCB200_EARG otherwise.
  * ldiagnos!=0 also accumulates the 0-D diagnostics on substep 1.
  * *dt (in/out): on substep 1 with ldt the new time step is returned. */
 int pcb200_substep(int isubstep, int full, int early_finalize, int ldiagnos, double *dt);
@@ -252,7 +253,10 @@ typedef struct pcb200_particle_params {
   int32_t ldragforce_gas_par;    /* back-reaction on the gas (:4443-4536) */
   int32_t lcoriolis_force_par;   /* dvvp_dt Coriolis term, uses pcb200_params.Omega (:3230) */
   int32_t ldt_adv_par;           /* particle advection CFL (dxxp_dt_pencil :3936) */
-  int32_t lcheck_exact_frontier; /* clamp ineargrid into the interior (particles_map.f90:940) */
+  int32_t lcheck_exact_frontier; /* particles_map.f90:940-943.  The device ALWAYS clamps ineargrid into the interior
+                                    (the behaviour of lcheck_exact_frontier=T); with F the reference stops with
+                                    fatal_error when round-off puts a particle one cell outside -- the device does
+                                    not reproduce that stop */
   int32_t reserved_i[8];
   double tausp;                  /* constant friction time (ldraglaw_epstein, get_frictiontime :5410) */
   double rhop_swarm;             /* mass density of one superparticle in a cell (get_rhopswarm, particles_sub.f90:950) */

@@ -39,6 +39,9 @@
 #ifndef PCB200_DLY_ACC
 #define PCB200_DLY_ACC 0       // 1: accumulator form for every variant (A/B timing)
 #endif
+#ifndef PCB200_DLY_WPROD
+#define PCB200_DLY_WPROD 32    // thread that requests the w tiles (0: the thread that requests the planes does both)
+#endif
 #ifndef PCB200_DLY_ZS
 #define PCB200_DLY_ZS 0        // 1: z+1..z+3 from the ring for every variant (A/B timing)
 #endif
@@ -288,15 +291,18 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     const int n = zb - NG + s;                // centre plane, interior-relative
     const bool more = s + NP < nstep;         // ring plane s+NP exists: issue it into the slot of plane s-1
     const bool morew = RW && NWBUF == 3 && s + 2 < nstep;   // w tiles of step s+2 into the buffer of step s-1
-    // both overwrite what step s-1 used: wait for "empty" of step s-1 (probe now, block after the stencils)
-    auto issue_all = [&]() __attribute__((always_inline)) {
-      if (more) { mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES); issue_plane(s + NP, cr == 0 ? NSD - 1 : cr - 1); }
-      if (morew) issue_w(s + 2, c3 == 0 ? 2 : c3 - 1);
+    // both overwrite what step s-1 used: wait for "empty" of step s-1 (probe now, block after the stencils).
+    // Two producers on two schedulers: thread 0 (warp 0) requests the plane, thread 32 (warp 1) the w tiles --
+    // the ~80 instructions of both in one warp made that warp the slowest of the CTA in every step.
+    const bool prodP = more && tid == 0, prodW = morew && tid == PCB200_DLY_WPROD;
+    auto issue_mine = [&]() __attribute__((always_inline)) {
+      if (prodP) { mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES); issue_plane(s + NP, cr == 0 ? NSD - 1 : cr - 1); }
+      if (prodW) issue_w(s + 2, c3 == 0 ? 2 : c3 - 1);
     };
     bool issued = true;
-    if ((more || morew) && tid == 0) {
+    if (prodP || prodW) {
       issued = s == 0 || mbar_test_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
-      if (issued) issue_all();
+      if (issued) issue_mine();
     }
     const bool doA = FULL || (s >= 3 && s < nzc + 3);   // phase A produces output (centre plane inside the chunk)
     const bool doB = FULL || s >= 6;                    // phase B finishes plane n-3
@@ -324,9 +330,9 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     HydroPend hp;
     hydro_pre<MAG, ENT, (AUXM > 0)>(acc, c, FULL ? n : min(max(n, 0), c.nz - 1), rhs, aux, hp);
     hydro_finish<MAG, ENT, (AUXM > 0), false>(c, hp, m, rhs, aux);     // Ohmic heating needs the whole J: phase B
-    if (tid == 0 && !issued) {
+    if (!issued) {
       mbar_wait(empty + ((s - 1) & 1), (unsigned)(((s - 1) >> 1) & 1));
-      issue_all();
+      issue_mine();
     }
     // ---- phase B: finish plane n-3 (du/dt; with magnetic+entropy also ds/dt) ----
     // ga..ge: the five groups loaded per step.  History form: D3(s-6), D2(s-1), D2(s-5), D1(s-2), D1(s-4).
