@@ -40,7 +40,7 @@
 #define PCB200_DLY_ACC 0       // 1: accumulator form for every variant (A/B timing)
 #endif
 #ifndef PCB200_DLY_WPROD
-#define PCB200_DLY_WPROD 32    // thread that requests the w tiles (0: the thread that requests the planes does both)
+#define PCB200_DLY_WPROD 0     // thread that requests the w tiles: 0 = the thread that requests the planes does both; 32 (warp 1, another scheduler) measured 1.9 % slower
 #endif
 #ifndef PCB200_DLY_ZS
 #define PCB200_DLY_ZS 0        // 1: z+1..z+3 from the ring for every variant (A/B timing)
@@ -292,8 +292,8 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
     const bool more = s + NP < nstep;         // ring plane s+NP exists: issue it into the slot of plane s-1
     const bool morew = RW && NWBUF == 3 && s + 2 < nstep;   // w tiles of step s+2 into the buffer of step s-1
     // both overwrite what step s-1 used: wait for "empty" of step s-1 (probe now, block after the stencils).
-    // Two producers on two schedulers: thread 0 (warp 0) requests the plane, thread 32 (warp 1) the w tiles --
-    // the ~80 instructions of both in one warp made that warp the slowest of the CTA in every step.
+    // One producer by default (PCB200_DLY_WPROD=0).  Splitting the ~80 producer instructions over two warps on two
+    // schedulers (thread 0 the plane, thread 32 the w tiles) measured 7.53 against 7.39 ms per 512^3 substep.
     const bool prodP = more && tid == 0, prodW = morew && tid == PCB200_DLY_WPROD;
     auto issue_mine = [&]() __attribute__((always_inline)) {
       if (prodP) { mbar_expect_tx(full + ((s + 1) & 1), BOX_BYTES); issue_plane(s + NP, cr == 0 ? NSD - 1 : cr - 1); }
