@@ -341,6 +341,36 @@ def test_gpu_reproduces_fluxrings_reference_out_double(pk, dev):
 
 # ---------------------------------------------------------------------------
 # production-size launch shapes (the benchmarked 16x64 tile grid, several z-chunks, element offsets ~1e9)
+def test_gpu_reproduces_helical_mhdturb_reference_out(pk, dev):
+    """The CUDA path (through the C ABI, device diagnostics, forcing kick on the device) against the reference's own
+    samples/helical-MHDturb/reference.out: forced isothermal MHD from the 'gaussian-noise' initial condition, the
+    reference's nr_f90 random stream for the wave vector, phase and e-vector of every kick (oracle/nr_f90.py supplies
+    the stream: test infrastructure).  Call order of the Fortran wrapper: substep 1 returns dt, the coefficients are
+    drawn with that dt (fact = force/ffnorm*sqrt(dt), forcing.f90:1741), the device applies the kick after substep 3.
+    Tolerance: 1.5 units of the last printed digit, the rule of the reference's test harness."""
+    from oracle import nr_f90
+    from tests.test_oracle_helical_mhdturb import check_rows, helical_mhdturb_setup, row_from_diag
+    P, zprof, grid, f, (nk, kav, kkx, kky, kkz), stream = helical_mhdturb_setup(pk)
+    dev.initialize_GPU(P, zprof)
+    dev.register_GPU(f)
+    dev.set_forcing(None)
+    rows, t = [], 0.0
+    for it in range(9):
+        diag = it % 2 == 0
+        dt = dev.rhs_GPU(f, 1, ldiagnos=diag)
+        if diag:
+            rows.append(row_from_diag(pk, P, t, dt, list(dev.diagnostics().values())))
+        phase, ik, phi = nr_f90.helical_draw(stream, nk)
+        dev.set_forcing(pk.setups.helical_forcing_coefs((kkx[ik - 1], kky[ik - 1], kkz[ik - 1]), phase, phi, dt,
+                                                        force=0.07, relhel=1.0, kav=kav))
+        dev.rhs_GPU(f, 2)
+        dev.rhs_GPU(f, 3)
+        t += dt
+    dev.set_forcing(None)
+    worst = check_rows(rows)
+    print("GPU vs helical-MHDturb reference.out: worst error / tolerance", worst)
+
+
 PROD_CASES = {
     # 512x512x64 isothermal MHD: the BENCH tile grid (16 x 64 tiles) with real z-chunking
     "mhd_512x512x64": lambda pk: pk.setups.make_params(512, 512, 64, magnetic=True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3),
