@@ -25,6 +25,9 @@ struct SnapWriter {
   int rc = 0; std::string err;
   int device = 0;
 
+  // a caller that exits with a snapshot in flight (no wait, no finalize): finish the file instead of std::terminate
+  ~SnapWriter() { if (th.joinable()) th.join(); }
+
   int fail_(const std::string &m) { rc = -4; err = m; return rc; }
 
   // worker: record 1 from the staging array, record 2 from `tail`
