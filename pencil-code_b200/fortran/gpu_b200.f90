@@ -423,6 +423,8 @@ contains
       real, dimension(:,:,:,:), intent(IN), target :: f
 !
       call check(pcb200_register(f),'register_GPU')
+!  kept by address, like registerGPU of the reference (astaroth/gpu_astaroth.cc:224-234): run.f90's f lives for the
+!  whole run; the pointer is only used for the download before a RELOAD re-creates the device buffers
       f_registered => f
 !
     endsubroutine register_GPU
