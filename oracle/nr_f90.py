@@ -117,3 +117,45 @@ def helical_draw(g, nk):
     ik = int(nk * (0.9999 * fran[1])) + 1           # Fortran integer conversion truncates; 1-based
     phi = g.draw() * 2 * math.pi
     return phase, ik, phi
+
+
+class MinStd:
+    """random_gen='min_std' (the default, general.f90:178): ran0, the 'Minimal Standard' generator of Lewis, Goodman
+    and Miller with one state word (general.f90:601-623); PUT/GET move that word (general.f90:551-555)."""
+    MASK = 123459876
+
+    def __init__(self):
+        self.state = 0
+        self.am = 1.0 / IM
+
+    def draw(self):
+        d = _s32(self.state ^ self.MASK)
+        k = int(d / IQ)                                   # Fortran integer division truncates toward zero
+        d = IA * (d - k * IQ) - IR * k
+        if d < 0:
+            d += IM
+        self.state = _s32(d ^ self.MASK)
+        return self.am * d
+
+    def draws(self, n):
+        return np.array([self.draw() for _ in range(n)])
+
+    def put(self, seed):
+        self.state = _s32(seed[0])
+
+    def get(self):
+        return [self.state, 0]
+
+
+def start_stream_min_std(iproc=0, seed0=1812):
+    """start.f90:383 with random_gen='min_std': rstate(1) = -((seed0-1812+1)*10+iproc), processor dependent"""
+    g = MinStd()
+    g.put([-((seed0 - 1812 + 1) * 10 + iproc), 0])
+    return g
+
+
+def run_stream_min_std(seed0=1812):
+    """start.f90:500-503 puts seed(1)=seed0 after the initial conditions; the snapshot carries it into run.x"""
+    g = MinStd()
+    g.put([seed0, 0])
+    return g

@@ -1,0 +1,56 @@
+"""A reference-held golden vector of a MULTI-PROCESS run: samples/turbulence/helical-MHDturb32-4procs/reference.out --
+forced isothermal helical MHD at 128^3 (nu=eta=2e-3, force=0.05, default cdt=0.9, cdtv=0.25, default random_gen=
+'min_std') run by the reference on 4 MPI processes (nprocy=2, nprocz=2: the layout that reproduces the file; the
+cparam.local shipped today says 1x4x8, which gives another random field -- six layouts tried, only 1x2x2 matches
+brms, abm and jbm at it=0).  Every process draws its own Gaussian-noise block, ghost zones included, from its own
+stream (seed -(10+iproc), start.f90:383); the global field assembled from those blocks and advanced by the
+SINGLE-DOMAIN oracle reproduces the 4-process run.  Together with tests/mgpu_check.py (every block decomposition of
+the CUDA path == single-domain oracle) this ties the multi-GPU path to a multi-process run of the reference.
+
+Columns checked: t, dt, urms, brms, abm, jbm, oum, epsM (= eta*mu0*<j^2>), rhom at it = 0, 5; tolerance: 1.5 units of
+the last printed digit (the reference harness).  epsK is not among the device diagnostics."""
+import math
+import os
+
+import numpy as np
+
+from tests.test_oracle_helical_mhdturb import printed_tolerance
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+COLS = {"t": 1, "dt": 2, "urms": 3, "brms": 4, "abm": 5, "jbm": 6, "oum": 7, "epsM": 9, "rhom": 10}
+
+
+def test_single_domain_oracle_reproduces_the_4_process_reference_run(pk, orc):
+    from oracle import nr_f90
+    N, nproc = 128, (1, 2, 2)
+    P, zprof, grid = pk.setups.make_params(N, N, N, magnetic=True, nu=2e-3, eta=2e-3, cdt=0.9, cdtv=0.25)
+    f = np.zeros((P.mvar, N + 6, N + 6, N + 6))
+    nx, ny, nz = N // nproc[0], N // nproc[1], N // nproc[2]
+    for iproc in range(nproc[0] * nproc[1] * nproc[2]):          # iproc = ipx + nprocx*(ipy + nprocy*ipz), mpicomm.f90:367-369
+        ipx, ipy, ipz = iproc % nproc[0], (iproc // nproc[0]) % nproc[1], iproc // (nproc[0] * nproc[1])
+        loc = np.zeros((P.mvar, nz + 6, ny + 6, nx + 6))
+        nr_f90.gaunoise_vect(nr_f90.start_stream_min_std(iproc), loc, 1e-4, P.iax - 1, P.iaz - 1)
+        f[:, 3 + ipz * nz:3 + (ipz + 1) * nz, 3 + ipy * ny:3 + (ipy + 1) * ny, 3 + ipx * nx:3 + (ipx + 1) * nx] = loc[:, 3:-3, 3:-3, 3:-3]
+    f = np.ascontiguousarray(np.pad(f[:, 3:-3, 3:-3, 3:-3], ((0, 0), (3, 3), (3, 3), (3, 3)), mode="wrap"))
+    nk, kav, kkx, kky, kkz = nr_f90.read_kdat(os.path.join(HERE, "golden", "helical-MHDturb.k.dat"))   # same k.dat in both samples
+    stream = nr_f90.run_stream_min_std()
+    gold = [ln.split() for ln in open(os.path.join(HERE, "golden", "helical-MHDturb32-4procs.reference.out")) if not ln.startswith("#")]
+    df = np.zeros_like(f)
+    nw, t, dt, rows = N ** 3, 0.0, 0.0, []
+    for it in range(6):
+        d = np.zeros(16)
+        dt_step = orc.timestep(f.copy(), df.copy(), P, dt, None, d)
+        if it % 5 == 0:
+            n = dict(zip(pk.abi.DIAG_NAMES, d))
+            rows.append({"t": t, "dt": dt_step, "urms": math.sqrt(n["u2sum"] / nw), "brms": math.sqrt(n["b2sum"] / nw),
+                         "abm": n["absum"] / nw, "jbm": n["jbsum"] / nw, "oum": n["ousum"] / nw,
+                         "epsM": P.eta * P.mu0 * n["j2sum"] / nw, "rhom": n["rhosum"] / nw})
+        phase, ik, phi = nr_f90.helical_draw(stream, nk)
+        frc = pk.setups.helical_forcing_coefs((kkx[ik - 1], kky[ik - 1], kkz[ik - 1]), phase, phi, dt_step,
+                                              force=0.05, relhel=1.0, kav=kav)
+        dt = orc.timestep(f, df, P, dt, frc, None)
+        t += dt
+    assert len(rows) == len(gold) == 2
+    for got, ref in zip(rows, gold):
+        for name, j in COLS.items():
+            assert abs(got[name] - float(ref[j])) <= printed_tolerance(ref[j]), (ref[0], name, got[name], ref[j])
