@@ -371,6 +371,45 @@ def test_gpu_reproduces_helical_mhdturb_reference_out(pk, dev):
     print("GPU vs helical-MHDturb reference.out: worst error / tolerance", worst)
 
 
+def test_gpu_reproduces_sod10_reference_out(pk, dev):
+    """The CUDA path against samples/1d-tests/sod_10/reference.out (Sod shock tube: entropy with chi-const conduction,
+    viscous heating, walls 'a'/'s' in x; see tests/test_oracle_sod.py).  The kernels want >= 6 points per direction, so the
+    tube is run as 400 x 6 x 6 with dy_1 = dz_1 = 0 like the host's one-point directions: fields uniform in y and z, all y/z
+    derivatives exactly zero, means unchanged.  t, dt, urms, rhom, ssm at it = 0, 100, 200, 300 to the printed digits."""
+    import math
+    from tests.test_oracle_helical_mhdturb import printed_tolerance
+    from tests.test_oracle_sod import read_table
+    P, zprof, grid = pk.setups.make_params(400, 6, 6, entropy=True, xyz0=(-4.0, 0.0, 0.0), Lxyz=(10.0, 1.0, 1.0), lperi=(0, 1, 1),
+                                           nu=0.02, chi=5e-4, iheatcond=pk.abi.HCOND["chi-const"], cdt=0.4, cdtv=0.25,
+                                           gamma=5.0 / 3.0, bcx=["a", "s", "s", "s", "s"])
+    P.dy_1 = 0.0
+    P.dz_1 = 0.0
+    prof = 0.5 * (1.0 + np.tanh(grid["x"] / 0.03))[None, None, :]
+    f = np.zeros((P.mvar, P.nz + 6, P.ny + 6, P.nx + 6))
+    f[P.ilnrho - 1] += math.log(10.0) * (1.0 - prof)
+    f[P.iss - 1] += -0.615 + (0.306 + 0.615) * prof
+    dev.initialize_GPU(P, zprof)
+    dev.register_GPU(f)
+    dev.set_forcing(None)
+    head, gold = read_table("sod_10")
+    col = {h: j for j, h in enumerate(head)}
+    nw, t, k = P.nx * P.ny * P.nz, 0.0, 0
+    for it in range(301):
+        diag = it % 100 == 0
+        dt = dev.rhs_GPU(f, 1, ldiagnos=diag)
+        if diag:
+            v = dev.diagnostics()
+            got = {"t": t, "dt": dt, "urms": math.sqrt(v["u2sum"] / nw), "rhom": v["rhosum"] / nw, "ssm": v["sssum"] / nw}
+            for nm, val in got.items():
+                tok = gold[k][col[nm]]
+                assert abs(val - float(tok)) <= printed_tolerance(tok), (it, nm, val, tok)
+            k += 1
+        dev.rhs_GPU(f, 2)
+        dev.rhs_GPU(f, 3)
+        t += dt
+    assert k == 4
+
+
 PROD_CASES = {
     # 512x512x64 isothermal MHD: the BENCH tile grid (16 x 64 tiles) with real z-chunking
     "mhd_512x512x64": lambda pk: pk.setups.make_params(512, 512, 64, magnetic=True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3),
