@@ -62,6 +62,11 @@ void pcref_rhs(const double *f, double *df, const pcb200_params *par,
  * df is scratch (mx*my*mz*mvar). *dt in/out. */
 void pcref_timestep(double *f, double *df, const pcb200_params *par,
                     const pcb200_forcing *frc, double *dt, double *diag);
+/* pcref_pencil.c: the same time step evaluated pencil-wise (timing arm of bench.py only; falls back to
+ * pcref_timestep where it does not apply or when diagnostics are requested) */
+int pcref_pencil_applies(const pcb200_params *par);
+void pcref_timestep_pencil(double *f, double *df, const pcb200_params *par,
+                           const pcb200_forcing *frc, double *dt, double *diag);
 
 /* forcing_hel application (forcing.f90:1968-2110) */
 void pcref_addforce(double *f, const pcb200_params *par, const pcb200_forcing *frc);

@@ -12,7 +12,7 @@ LIB = os.path.join(_HERE, "libpcref.so")
 
 
 def build(force=False):
-    srcs = [os.path.join(_HERE, n) for n in ("pcref.c", "pcref_particles.c", "pcref.h")]
+    srcs = [os.path.join(_HERE, n) for n in ("pcref.c", "pcref_particles.c", "pcref_pencil.c", "pcref.h")]
     if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(q) for q in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return LIB
@@ -53,6 +53,10 @@ class Oracle:
         L.pcref_rhs.restype = None
         L.pcref_timestep.argtypes = [p, p, C.POINTER(abi.Params), C.POINTER(abi.Forcing), C.POINTER(d), p]
         L.pcref_timestep.restype = None
+        L.pcref_timestep_pencil.argtypes = [p, p, C.POINTER(abi.Params), C.POINTER(abi.Forcing), C.POINTER(d), p]
+        L.pcref_timestep_pencil.restype = None
+        L.pcref_pencil_applies.argtypes = [C.POINTER(abi.Params)]
+        L.pcref_pencil_applies.restype = i
         L.pcref_addforce.argtypes = [p, C.POINTER(abi.Params), C.POINTER(abi.Forcing)]
         L.pcref_addforce.restype = None
         L.pcref_set_zprofile.argtypes = [i, p, i]
@@ -119,6 +123,17 @@ class Oracle:
                                 C.byref(frc) if frc is not None else None, C.byref(d),
                                 diag.ctypes.data if diag is not None else None)
         return d.value
+
+    def timestep_pencil(self, f, df, par, dt=0.0, frc=None):
+        """the same time step evaluated pencil-wise like the reference's mn-loop (pcref_pencil.c): for TIMING the CPU arm;
+        falls back to timestep() where it does not apply"""
+        d = C.c_double(dt)
+        self.lib.pcref_timestep_pencil(f.ctypes.data, df.ctypes.data, C.byref(par),
+                                       C.byref(frc) if frc is not None else None, C.byref(d), None)
+        return d.value
+
+    def pencil_applies(self, par):
+        return bool(self.lib.pcref_pencil_applies(C.byref(par)))
 
     def num_threads(self):
         return self.lib.pcref_num_threads()
