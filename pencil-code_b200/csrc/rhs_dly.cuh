@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(NTHR, 1) rhs_dly(SubstepArgs a, const __grid_c
   // tmap_wr has a one-variable box (lnrho at plane n, ss at plane n-3) and A comes through tmap_wu.
   static_assert(AUXM < 2, "full diagnostics run through rhs_tma");
   typedef DlyCfg<MAG, ENT> Cfg;
-  constexpr int NC = Cfg::NC, NF = Cfg::NF, NSD = Cfg::NSD, NP = Cfg::NP, PG = Cfg::PG, NWBUF = Cfg::NWBUF, WD = Cfg::WD;
+  constexpr int NC = Cfg::NC, NF = Cfg::NF, NSD = Cfg::NSD, NP = Cfg::NP, PG = Cfg::PG, NWBUF = Cfg::NWBUF;
   constexpr bool ACCF = Cfg::ACCF, ME = MAG && ENT;
   const DevPar &c = c_par;
   extern __shared__ __align__(128) unsigned char smem_raw[];
