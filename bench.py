@@ -136,8 +136,7 @@ def run_reference(args):
     f = bench_fields(pk, args, P, grid)
     df = np.zeros_like(f)
     dt = 0.0
-    # pencil-wise evaluation like the reference's mn-loop where it applies (hydro/MHD without the entropy module),
-    # else the point-wise port
+    # pencil-wise evaluation like the reference's mn-loop where it applies (BASELINE configs 1-4), else the point-wise port
     for _ in range(args.warmup):
         dt = orc.timestep_pencil(f, df, P, dt)
     t0 = time.perf_counter()

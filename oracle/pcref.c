@@ -36,6 +36,12 @@ void pcref_set_zprofile(int which, const double *prof, int nz)
 }
 
 /* bench.py --impl reference under torchrun inherits OMP_NUM_THREADS=1: the CPU arm sets the count itself */
+/* the profile set by pcref_set_zprofile (pcref_pencil.c reads the same arrays) */
+const double *pcref_get_zprofile(int which)
+{
+  return (which >= 0 && which < PCB200_NPROF) ? g_zprof[which] : 0;
+}
+
 void pcref_set_num_threads(int n)
 {
 #ifdef _OPENMP

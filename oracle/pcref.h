@@ -65,6 +65,7 @@ void pcref_timestep(double *f, double *df, const pcb200_params *par,
 /* pcref_pencil.c: the same time step evaluated pencil-wise (timing arm of bench.py only; falls back to
  * pcref_timestep where it does not apply or when diagnostics are requested) */
 int pcref_pencil_applies(const pcb200_params *par);
+const double *pcref_get_zprofile(int which);
 void pcref_timestep_pencil(double *f, double *df, const pcb200_params *par,
                            const pcb200_forcing *frc, double *dt, double *diag);
 
