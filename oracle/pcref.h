@@ -84,6 +84,7 @@ void pcref_particles_sort(double *fp, double *dfp, int32_t *ipar, int32_t *inear
                           const pcb200_params *par, const pcb200_particle_params *pp);
 void pcref_particles_map_xxp_grid(const double *fp, const int32_t *ineargrid, double *np, double *rhop,
                                   const pcb200_params *par, const pcb200_particle_params *pp);
+void pcref_particles_fixture(int interp_cic, const double *ap_by_ipar, long nap, double rhopmat, const int32_t *ipar);
 void pcref_particles_pde(const double *f, double *df, const double *fp, double *dfp, const int32_t *ineargrid,
                          const pcb200_params *par, const pcb200_particle_params *pp, int lfirst, double *dt1_max);
 void pcref_timestep_particles(double *f, double *df, const pcb200_params *par, const pcb200_forcing *frc,

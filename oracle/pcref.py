@@ -72,6 +72,8 @@ class Oracle:
         L.pcref_particles_map_xxp_grid.argtypes = [p, p, p, p, PA, PP]
         L.pcref_particles_pde.argtypes = [p, p, p, p, p, PA, PP, i, C.POINTER(d)]
         L.pcref_timestep_particles.argtypes = [p, p, PA, C.POINTER(abi.Forcing), C.POINTER(d), p, PP, p, p, p, p, p, p, p, p]
+        L.pcref_particles_fixture.argtypes = [i, p, C.c_long, d, p]
+        L.pcref_particles_fixture.restype = None
         for name in ("pcref_particles_boundconds", "pcref_particles_map_nearest_grid", "pcref_setup_imn_array",
                      "pcref_particles_sort", "pcref_particles_map_xxp_grid", "pcref_particles_pde",
                      "pcref_timestep_particles"):
@@ -166,6 +168,16 @@ class Oracle:
         self.lib.pcref_particles_pde(f.ctypes.data, df.ctypes.data, st.fp.ctypes.data, st.dfp.ctypes.data,
                                      st.ineargrid.ctypes.data, C.byref(par), C.byref(pp), int(lfirst), C.byref(d))
         return d.value
+
+    def particles_fixture(self, st=None, ap_by_ipar=None, rhopmat=0.0, interp_cic=False):
+        """options of the reference fixture samples/ParticlesCaustics (CIC interpolation, pure Stokes drag with the radii
+        of particles_radius, looked up by st.ipar); call without arguments to switch them off again.  The arrays must
+        stay alive while the options are on."""
+        if st is None:
+            self.lib.pcref_particles_fixture(0, None, 0, 0.0, None)
+        else:
+            self.lib.pcref_particles_fixture(int(interp_cic), ap_by_ipar.ctypes.data if ap_by_ipar is not None else None,
+                                             0 if ap_by_ipar is None else ap_by_ipar.size, float(rhopmat), st.ipar.ctypes.data)
 
     def timestep_particles(self, f, df, par, pp, st, dt=0.0, frc=None, diag=None):
         d = C.c_double(dt)

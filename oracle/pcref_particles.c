@@ -1,11 +1,17 @@
 /* pcref_particles.c -- CPU restatement of the dust-particle part of the hot path.
  *
- * TEST INFRASTRUCTURE ONLY (see pcref.c).  Parity: UNPINNED -- the reference ships
- * no double-precision golden output for a particle run inside the path
- * (samples/convective-overstability-particles needs shear, shock, self-gravity and
- * sink particles); this file is checked by known-answer tests (drag relaxation,
- * momentum conservation, TSC partition of unity, index arithmetic) in
- * tests/test_oracle_particles.py.
+ * TEST INFRASTRUCTURE ONLY (see pcref.c).  Parity: PINNED IN PART.  The particle
+ * integration (initial state from the nr_f90 streams of 4 processes, boundconds,
+ * nearest grid point, pencil sort, drag acceleration, drag time step, RK3 update)
+ * reproduces every printed digit of samples/ParticlesCaustics/reference.out
+ * (xp2m, yp2m, zp2m, vprms, dt over 8 steps; tests/test_oracle_particles_caustics.py)
+ * with the two settings of that sample this file carries for the purpose
+ * (pcref_particles_fixture: CIC interpolation, pure Stokes drag).  The TSC
+ * assignment, the quadratic-spline interpolation and the back-reaction on the gas
+ * are NOT pinned by a reference file (samples/convective-overstability-particles and
+ * streaming_instability need shear, shock, self-gravity, sink particles); they are
+ * checked by known-answer tests (drag relaxation, momentum conservation, TSC
+ * partition of unity, index arithmetic) in tests/test_oracle_particles.py.
  *
  * Follows, routine by routine (all under /root/reference/src):
  *   boundconds_particles   particles_sub.f90:135-330      periodic wrap
@@ -263,6 +269,43 @@ static void interp_qspline(const double *f, const pcb200_params *par, int ivar1,
   }
 }
 
+/* ---- options of the reference fixture samples/ParticlesCaustics (checker only; the shipped library has the
+ * quadratic spline and a constant friction time): interp_pol_uu='cic' and ldraglaw_purestokes with the radii of
+ * particles_radius.  Set once by the test that replays the fixture, off by default. ---- */
+static int g_fix_cic = 0;
+static const double *g_fix_ap = 0;         /* radius by particle identity ipar (1-based) */
+static long g_fix_nap = 0;
+static double g_fix_rhopmat = 0.0;
+static const int32_t *g_fix_ipar = 0;      /* ipar of the state pcref_particles_pde is called on */
+void pcref_particles_fixture(int interp_cic, const double *ap_by_ipar, long nap, double rhopmat, const int32_t *ipar)
+{
+  g_fix_cic = interp_cic; g_fix_ap = ap_by_ipar; g_fix_nap = ap_by_ipar ? nap : 0; g_fix_rhopmat = rhopmat; g_fix_ipar = ipar;
+}
+
+/* interpolate_linear_range (particles_map.f90:112-287), equidistant grid, all three directions present */
+static void interp_linear(const double *f, const pcb200_params *par, int ivar1, int nvar, const double *xxp, const int *inear, double *gp)
+{
+  const long mw = (long)(par->nx + 2 * NG) * (par->ny + 2 * NG) * (par->nz + 2 * NG);
+  int ix0 = inear[0], iy0 = inear[1], iz0 = inear[2];
+  if (gx(par, 0, ix0) > xxp[0]) ix0 = ix0 - 1;
+  if (gx(par, 1, iy0) > xxp[1]) iy0 = iy0 - 1;
+  if (gx(par, 2, iz0) > xxp[2]) iz0 = iz0 - 1;
+  const double xp0 = xxp[0] - gx(par, 0, ix0), yp0 = xxp[1] - gx(par, 1, iy0), zp0 = xxp[2] - gx(par, 2, iz0);
+  const double dx1 = par->dx_1, dy1 = par->dy_1, dz1 = par->dz_1;
+  const double dxdy1 = dx1 * dy1, dxdz1 = dx1 * dz1, dydz1 = dy1 * dz1, dxdydz1 = dx1 * dy1 * dz1;
+  for (int j = 0; j < nvar; j++) {
+    const double *g = f + (long)(ivar1 + j) * mw;
+    const double g1 = g[cell(par, ix0, iy0, iz0)], g2 = g[cell(par, ix0 + 1, iy0, iz0)];
+    const double g3 = g[cell(par, ix0, iy0 + 1, iz0)], g4 = g[cell(par, ix0 + 1, iy0 + 1, iz0)];
+    const double g5 = g[cell(par, ix0, iy0, iz0 + 1)], g6 = g[cell(par, ix0 + 1, iy0, iz0 + 1)];
+    const double g7 = g[cell(par, ix0, iy0 + 1, iz0 + 1)], g8 = g[cell(par, ix0 + 1, iy0 + 1, iz0 + 1)];
+    gp[j] = g1 + xp0 * dx1 * (-g1 + g2) + yp0 * dy1 * (-g1 + g3) + zp0 * dz1 * (-g1 + g5) +
+            xp0 * yp0 * dxdy1 * (g1 - g2 - g3 + g4) + xp0 * zp0 * dxdz1 * (g1 - g2 - g5 + g6) +
+            yp0 * zp0 * dydz1 * (g1 - g3 - g5 + g7) +
+            xp0 * yp0 * zp0 * dxdydz1 * (-g1 + g2 + g3 - g4 + g5 - g6 - g7 + g8);
+  }
+}
+
 /* dxxp_dt_pencil + dvvp_dt_pencil over all pencils (particles_dust.f90:3918-3977, 3979-4911),
  * then dxxp_dt, dvvp_dt (:3120-3197, :3199-3250) and fold_df(df,iux,iuz) (equ.f90:407-413).
  * f: state with valid ghost zones; df: gas RHS register (mx,my,mz,mvar), receives the
@@ -272,7 +315,7 @@ void pcref_particles_pde(const double *f, double *df, const double *fp, double *
 {
   const long M = pp->mpar_loc, N = pp->npar_loc;
   const long mw = (long)(par->nx + 2 * NG) * (par->ny + 2 * NG) * (par->nz + 2 * NG);
-  const double tausp1 = pp->tausp != 0.0 ? 1.0 / pp->tausp : 0.0;
+  double tausp1 = pp->tausp != 0.0 ? 1.0 / pp->tausp : 0.0;
   const double *lnrho = f + (long)(par->ilnrho - 1) * mw;
   const int iux = par->iux - 1;
   const int ldt = lfirst && par->ldt;
@@ -291,7 +334,14 @@ void pcref_particles_pde(const double *f, double *df, const double *fp, double *
     }
     if (pp->ldragforce_dust_par) {
       double uup[3];
-      interp_qspline(f, par, iux, xxp, inear, uup);                       /* :4226 */
+      if (g_fix_cic) interp_linear(f, par, iux, 3, xxp, inear, uup);
+      else interp_qspline(f, par, iux, xxp, inear, uup);                  /* :4226 */
+      if (g_fix_nap) {                                                    /* calc_draglaw_purestokes :6314-6362 */
+        double lr;
+        interp_linear(f, par, par->ilnrho - 1, 1, xxp, inear, &lr);       /* interpolate_quantities, particles_map.f90:2151-2158 */
+        const double interp_rho = exp(lr), dia = 2.0 * g_fix_ap[g_fix_ipar[k] - 1];
+        tausp1 = 18.0 * par->nu / ((g_fix_rhopmat / interp_rho) * (dia * dia));
+      }
       double dragforce[3];
       for (int j = 0; j < 3; j++) dragforce[j] = -tausp1 * (vvp[j] - uup[j]);      /* :4264 */
       for (int j = 0; j < 3; j++) dfp[(IVPX + j) * M + k] = dfp[(IVPX + j) * M + k] + dragforce[j];   /* :4275 */
