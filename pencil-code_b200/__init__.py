@@ -5,5 +5,5 @@ modules mirror that host interface for tests and the bench.
 
 The directory name is not a Python identifier; load it through
 `__graft_entry__.package()` (registers it as `pencil_code_b200`)."""
-from . import abi, gpu, setups  # noqa: F401
+from . import abi, gpu, setups, snapshot  # noqa: F401
 from .gpu import GPU, PCB200Error, load_library  # noqa: F401

@@ -53,6 +53,22 @@ def read_var(path, mx, my, mz, mvar, dtype=np.float64):
     return out
 
 
+ID_BLOCK_PERSISTENT, ID_RECORD_RANDOM_SEEDS = 2000, 1          # record_types.h:13,16
+
+
+def read_persist(path):
+    """the persistent block that follows the two snapshot records (io_dist.f90:351-405 init_write_persist /
+    write_persist_id, read side :772-846): int32 2000, then pairs of records (id, payload), closed by 2000 again.
+    -> {id: payload bytes}; id 1 = the random-number state run.x restores (persist.f90:156-160)."""
+    recs = read_records(path)[2:]
+    ids = [struct.unpack("<i", r)[0] if len(r) == 4 else None for r in recs]
+    if not recs:
+        return {}
+    if ids[0] != ID_BLOCK_PERSISTENT or ids[-1] != ID_BLOCK_PERSISTENT or len(recs) % 2:
+        raise ValueError(f"{path}: persistent block not framed by {ID_BLOCK_PERSISTENT}")
+    return {ids[k]: recs[k + 1] for k in range(1, len(recs) - 1, 2)}
+
+
 def _write_record(fh, payload, rec_max=FREC_MAX):
     total, off, first = len(payload), 0, True
     while True:

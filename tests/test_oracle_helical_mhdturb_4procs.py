@@ -8,21 +8,33 @@ SINGLE-DOMAIN oracle reproduces the 4-process run.  Together with tests/mgpu_che
 the CUDA path == single-domain oracle) this ties the multi-GPU path to a multi-process run of the reference.
 
 Columns checked: t, dt, urms, brms, abm, jbm, oum, epsM (= eta*mu0*<j^2>), rhom at it = 0, 5; tolerance: 1.5 units of
-the last printed digit (the reference harness).  epsK is not among the device diagnostics."""
+the last printed digit (the reference harness).  epsK is not among the device diagnostics.
+
+Second file, same physics on 32 processes: samples/turbulence/helical-MHDturb-nopart/reference.out (nprocy=4, nprocz=8 as
+its cparam.local says) -- the 32 per-process noise blocks give brms = 5.400e-3 at it=0 where the 4-process run has
+5.398e-3; columns t, dt, urms, brms, epsM, rhom."""
 import math
 import os
 
 import numpy as np
+import pytest
 
 from tests.test_oracle_helical_mhdturb import printed_tolerance
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-COLS = {"t": 1, "dt": 2, "urms": 3, "brms": 4, "abm": 5, "jbm": 6, "oum": 7, "epsM": 9, "rhom": 10}
+RUNS = {
+    "4procs": ((1, 2, 2), "helical-MHDturb32-4procs.reference.out",
+               {"t": 1, "dt": 2, "urms": 3, "brms": 4, "abm": 5, "jbm": 6, "oum": 7, "epsM": 9, "rhom": 10}),
+    "nopart_32procs": ((1, 4, 8), "helical-MHDturb-nopart.reference.out",
+                       {"t": 1, "dt": 2, "urms": 3, "brms": 4, "epsM": 6, "rhom": 7}),
+}
 
 
-def test_single_domain_oracle_reproduces_the_4_process_reference_run(pk, orc):
+@pytest.mark.parametrize("run", list(RUNS))
+def test_single_domain_oracle_reproduces_the_multi_process_reference_run(pk, orc, run):
     from oracle import nr_f90
-    N, nproc = 128, (1, 2, 2)
+    nproc, golden, COLS = RUNS[run]
+    N = 128
     P, zprof, grid = pk.setups.make_params(N, N, N, magnetic=True, nu=2e-3, eta=2e-3, cdt=0.9, cdtv=0.25)
     f = np.zeros((P.mvar, N + 6, N + 6, N + 6))
     nx, ny, nz = N // nproc[0], N // nproc[1], N // nproc[2]
@@ -34,7 +46,7 @@ def test_single_domain_oracle_reproduces_the_4_process_reference_run(pk, orc):
     f = np.ascontiguousarray(np.pad(f[:, 3:-3, 3:-3, 3:-3], ((0, 0), (3, 3), (3, 3), (3, 3)), mode="wrap"))
     nk, kav, kkx, kky, kkz = nr_f90.read_kdat(os.path.join(HERE, "golden", "helical-MHDturb.k.dat"))   # same k.dat in both samples
     stream = nr_f90.run_stream_min_std()
-    gold = [ln.split() for ln in open(os.path.join(HERE, "golden", "helical-MHDturb32-4procs.reference.out")) if not ln.startswith("#")]
+    gold = [ln.split() for ln in open(os.path.join(HERE, "golden", golden)) if not ln.startswith("#")]
     df = np.zeros_like(f)
     nw, t, dt, rows = N ** 3, 0.0, 0.0, []
     for it in range(6):
