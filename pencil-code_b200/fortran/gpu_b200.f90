@@ -211,6 +211,7 @@ contains
       character(len=128) :: idstr
       integer :: i, local_rank
 !
+      id=c_null_char
       local_rank=mod(iproc,8)        ! ranks are placed node-contiguously by mpirun
       call check(pcb200_init(int(local_rank,c_int)),'gpu_init')
       if (ncpus>1) then
@@ -393,13 +394,23 @@ contains
 !
 !  particles_dust run parameters the device needs (particles_dust.f90:59-123,
 !  particles_cdata.f90): constant friction time, TSC particle-mesh scheme.
+!  tausp, cdtp, cdtp_drag and the four switches are private to module Particles (particles.h exports
+!  routines only): they arrive through pushpars2c, which fortran/host.patch adds to particles_dust.f90
+!  (and as an empty routine to noparticles.f90) the way viscosity.f90:2951 does it.
 !
       use Particles_cdata
-      use Particles, only: tausp, cdtp, cdtp_drag, ldragforce_dust_par, ldragforce_gas_par, &
-                           lcoriolis_force_par, ldt_adv_par
+      use Particles, only: particles_pars => pushpars2c
 !
       type(pcb200_particle_params) :: pp
+      integer(KIND=ikind8), dimension(7) :: p_par
+      real :: tausp, cdtp, cdtp_drag
+      logical :: ldragforce_dust_par, ldragforce_gas_par, lcoriolis_force_par, ldt_adv_par
 !
+      call particles_pars(p_par)
+      if (p_par(1)==0) call fatal_error('initialize_GPU','particles on the GPU need PARTICLES = particles_dust')
+      tausp=real_at(p_par(1)); cdtp=real_at(p_par(2)); cdtp_drag=real_at(p_par(3))
+      ldragforce_dust_par=logical_at(p_par(4)); ldragforce_gas_par=logical_at(p_par(5))
+      lcoriolis_force_par=logical_at(p_par(6)); ldt_adv_par=logical_at(p_par(7))
       if (.not.lparticlemesh_tsc .or. .not.linterpolate_spline) &
           call fatal_error('initialize_GPU','particles on the GPU need lparticlemesh_tsc=T, linterpolate_spline=T')
       pp%abi_version=PCB200_ABI_VERSION
@@ -420,7 +431,7 @@ contains
 !
 !  run.f90:223 -- hand over the address of f once (aliased, never freed).
 !
-      real, dimension(:,:,:,:), intent(IN), target :: f
+      real, dimension(:,:,:,:), intent(IN), target, contiguous :: f     ! contiguous: the address of f itself, no copy-in
 !
       call check(pcb200_register(f),'register_GPU')
 !  kept by address, like registerGPU of the reference (astaroth/gpu_astaroth.cc:224-234): run.f90's f lives for the
@@ -443,7 +454,8 @@ contains
 !  cdata:dt and t (timestep.f90:152-190) stay right.
 !
       use Forcing, only: forcing_pars_hel
-      use Particles_cdata, only: fp, ipar, npar_loc
+      use Particles_cdata, only: ipar
+      use Particles_main, only: fp          ! public through fortran/host.patch (particles_main.h exports routines only)
 !
       real, dimension (mx,my,mz,mfarray), intent(INOUT) :: f
       integer,                            intent(IN)    :: isubstep
@@ -496,6 +508,7 @@ contains
 !  ineargrid, the pencil ranges k1_imn/k2_imn and the aux fields np, rhop.
 !
       use Particles_cdata
+      use Particles_main, only: fp, dfp, ineargrid      ! public through fortran/host.patch
 !
       real, dimension (mx,my,mz,mfarray), intent(INOUT) :: f
 !

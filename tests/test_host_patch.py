@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = "/root/reference"
 PATCH = os.path.join(ROOT, "pencil-code_b200", "fortran", "host.patch")
 FILES = ["entropy.f90", "magnetic.f90", "viscosity.f90", "hydro.f90", "equ.f90", "timestep.f90", "noentropy.f90", "nomagnetic.f90",
-         "noforcing.f90"]
+         "noforcing.f90", "particles_dust.f90", "noparticles.f90", "particles_main.f90", "noparticles_main.f90"]
 
 
 @pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")) or shutil.which("patch") is None, reason="reference tree or patch(1) not here")
@@ -33,3 +33,118 @@ def test_wrapper_only_imports_what_the_reference_exports():
                 "use energy, only: lupw_ss"):
         assert bad not in src, bad
     assert "viscosity_pars => pushpars2c" in src and "energy_pars => pushpars2c" in src and "magnetic_pars => pushpars2c" in src
+
+
+# module of gpu_b200.f90's `use` statements -> the source files that can fill that slot in a build the wrapper supports
+MODULE_FILES = {
+    "equationofstate": ["eos_idealgas.f90"], "hydro": ["hydro.f90"], "density": ["density.f90"],
+    "viscosity": ["viscosity.f90"], "magnetic": ["magnetic.f90", "nomagnetic.f90"], "energy": ["entropy.f90", "noentropy.f90"],
+    "gravity": ["gravity_simple.f90", "nogravity.f90"], "forcing": ["forcing.f90", "noforcing.f90"], "mpicomm": ["mpicomm.f90", "nompicomm.f90"],
+    "particles": ["particles_dust.f90", "noparticles.f90"], "particles_main": ["particles_main.f90", "noparticles_main.f90"],
+    "particles_cdata": ["particles_cdata.f90"], "general": ["general.f90"], "messages": ["messages.f90"],
+}
+
+
+def _public_names(path):
+    """names a module file makes public: None when the module has no `private` default (everything is public)"""
+    import re
+    src = open(path, errors="replace").read()
+    head = src.split("\n  contains")[0] if "\n  contains" in src else src.split("\ncontains")[0]
+    text = head
+    for inc in re.findall(r"include\s+'([^']+)'", head):
+        ip = os.path.join(os.path.dirname(path), inc)
+        if os.path.exists(ip):
+            text += "\n" + open(ip, errors="replace").read()
+    text = re.sub(r"!.*", "", text)
+    text = re.sub(r"&\s*\n\s*&?", " ", text)
+    if not re.search(r"^\s*private\s*$", text, re.M | re.I):
+        return None
+    names = set()
+    for m in re.finditer(r"^\s*public\s*::\s*(.*)$", text, re.M | re.I):
+        names.update(n.strip().lower() for n in m.group(1).split(",") if n.strip())
+    for m in re.finditer(r"^[^\n]*,\s*public\b[^\n]*::\s*(.*)$", text, re.M | re.I):           # attribute form
+        names.update(re.match(r"\w+", n.strip()).group(0).lower() for n in m.group(1).split(",") if n.strip())
+    return names
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")) or shutil.which("patch") is None, reason="reference tree or patch(1) not here")
+def test_every_name_the_wrapper_imports_is_public_in_the_patched_host(tmp_path):
+    """every `use M, only: ...` of gpu_b200.f90 against the public list of every source file that can fill slot M
+    (the module's own `public ::` lines + its include'd *.h), after host.patch"""
+    import re
+    os.makedirs(tmp_path / "src")
+    for f in os.listdir(os.path.join(REF, "src")):
+        if f.endswith((".f90", ".h")):
+            shutil.copy(os.path.join(REF, "src", f), tmp_path / "src" / f)
+    for f in os.listdir(tmp_path / "src"):
+        os.chmod(tmp_path / "src" / f, 0o644)
+    r = subprocess.run(["patch", "-p1", "-i", PATCH], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    src = open(os.path.join(ROOT, "pencil-code_b200", "fortran", "gpu_b200.f90")).read()
+    src = re.sub(r"!.*", "", src)
+    src = re.sub(r"&\s*\n\s*&?", " ", src)
+    uses = re.findall(r"^\s*use\s+(\w+)\s*,\s*only\s*:\s*(.*)$", src, re.M | re.I)
+    assert len(uses) >= 12
+    missing = []
+    for mod, names in uses:
+        mod = mod.lower()
+        if mod == "cdata":
+            continue
+        assert mod in MODULE_FILES, mod
+        for item in names.split(","):
+            name = item.split("=>")[-1].strip().lower()                  # local => remote
+            for f in MODULE_FILES[mod]:
+                pub = _public_names(str(tmp_path / "src" / f))
+                if pub is not None and name not in pub:
+                    missing.append((mod, name, f))
+    assert not missing, missing
+    # whole-module imports only of modules without a private default
+    for mod in re.findall(r"^\s*use\s+(\w+)\s*$", src, re.M | re.I):
+        if mod.lower() in ("cdata",):
+            continue
+        assert mod.lower() in MODULE_FILES, mod
+        for f in MODULE_FILES[mod.lower()]:
+            assert _public_names(str(tmp_path / "src" / f)) is None, (mod, f)
+
+
+def test_fortran_mirrors_of_the_abi_structs_match_the_header():
+    """type, bind(C) :: pcb200_params / pcb200_particle_params / pcb200_forcing of gpu_b200.f90 against include/pcb200.h:
+    same members in the same order, integer vs real, array extents (reversed: Fortran is column-major)"""
+    import re
+    h = open(os.path.join(ROOT, "include", "pcb200.h")).read()
+    f = open(os.path.join(ROOT, "pencil-code_b200", "fortran", "gpu_b200.f90")).read()
+    consts = {k: v for k, v in re.findall(r"#define\s+(PCB200_\w+)\s+(\d+)", h)}
+
+    def c_members(name):
+        body = re.search(r"typedef struct " + name + r" \{(.*?)\} " + name + ";", h, re.S).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        out = []
+        for decl in body.split(";"):
+            if not decl.strip():
+                continue
+            ctype, rest = decl.strip().split(None, 1)
+            for v in rest.split(","):
+                m = re.match(r"\s*(\w+)((?:\[[^\]]+\])*)", v)
+                dims = [consts.get(d.strip(), d.strip()) for d in re.findall(r"\[([^\]]+)\]", m.group(2))]
+                out.append(("integer" if "int" in ctype else "real", m.group(1).lower(), dims))
+        return out
+
+    def f_members(name):
+        body = re.search(r"type, bind\(C\) :: " + name + r"\n(.*?)endtype", f, re.S).group(1)
+        fconst = {k.upper(): v for k, v in re.findall(r"(PCB200_\w+)=(\d+)", f)}
+        out = []
+        for ln in body.splitlines():
+            ln = ln.split("!")[0].strip()
+            if not ln:
+                continue
+            ftype, rest = ln.split("::")
+            for n, d in re.findall(r"(\w+)(\([^)]*\))?", rest):
+                dims = [fconst.get(x.strip().upper(), x.strip()) for x in d.strip("()").split(",")] if d else []
+                out.append(("integer" if ftype.strip().startswith("integer") else "real", n.lower(), dims[::-1]))
+        return out
+
+    for name in ("pcb200_params", "pcb200_particle_params", "pcb200_forcing"):
+        c, fm = c_members(name), f_members(name)
+        assert len(c) == len(fm) and len(c) > 3, (name, len(c), len(fm))
+        for a, b in zip(c, fm):
+            assert a == b, (name, a, b)
