@@ -6,6 +6,9 @@ golden time series samples/conv-slab/reference.out.double).
   ss   : 'piecew-poly'  entropy.f90:1628-1650 + polytropic_ss_z (entropy.f90:1849-1925)
   uu   : 'up-down'      hydro.f90:2189-2203
 Parameters: samples/conv-slab/start.in.
+
+Also: initss='mixinglength' of samples/2d-tests/conv-slab-MLT (entropy.f90:2108-2218 mixinglength, :7678-7741 strat_MLT,
+sub.f90:6092-6132 interp1), see mixinglength_stratification below.
 """
 import math
 
@@ -149,3 +152,71 @@ def fluxrings_initial_condition(P, grid, *, amplaa=1.0,
     g = np.zeros_like(f)                     # start.x fills the interior only
     g[:, 3:-3, 3:-3, 3:-3] = f[:, 3:-3, 3:-3, 3:-3]
     return g
+
+
+# ---------------------------------------------------------------------------
+# samples/2d-tests/conv-slab-MLT: initss='mixinglength'
+# ---------------------------------------------------------------------------
+def _interp1_descending(r, fr, r0):
+    """interp1(r,fr,nr,r0,ldescending=.true.) (sub.f90:6092-6132): linear interpolation in the reversed arrays"""
+    r1, fr1 = r[::-1], fr[::-1]
+    if r0 == r1[0]:
+        return fr1[0]
+    if r0 > r1[-1]:
+        return fr1[-1]
+    i = 0
+    while True:                      # do while (istop /= 1): if (r1(i) >= r0) istop=1; i=i+1
+        stop = r1[i] >= r0
+        i += 1
+        if stop:
+            break
+    i1, i2 = i - 2, i - 1            # Fortran i-2, i-1 with the 1-based i one past the hit
+    return (fr1[i1] * (r1[i2] - r0) + fr1[i2] * (r0 - r1[i1])) / (r1[i2] - r1[i1])
+
+
+def strat_MLT(rhotop, flux, *, nzgrid, ztop, dz, z1, z2, gravz, gamma, cs2top, mpoly0, mpoly1, alpha_MLT=1.5):
+    """entropy.f90:7678-7741: integrate temperature and ln rho downwards from the top with the mixing-length gradient
+    del = delad + alpha_MLT*(Fconv/(rho cs^3))^(2/3) in z1 <= z <= z2, the polytrope 1/(mpoly1+1) below, isothermal above.
+    -> lnrhom, tempm (index 0 = top), rho at z1"""
+    gamma_m1 = gamma - 1.0
+    lnrhom, tempm, zz = np.zeros(nzgrid), np.zeros(nzgrid), np.zeros(nzgrid)
+    lnrhom[0], tempm[0], zz[0] = math.log(rhotop), cs2top / gamma_m1, ztop
+    polyad, delad = 1.0 / gamma_m1, 1.0 - 1.0 / gamma
+    fc = (1.0 - delad * (mpoly0 + 1.0)) * flux
+    for iz in range(1, nzgrid):
+        zm = ztop - iz * dz
+        zz[iz] = zm
+        if zm < z1:
+            dl = 1.0 / (mpoly1 + 1.0)
+        elif zm <= z2:
+            dl = delad + alpha_MLT * (fc / (math.exp(lnrhom[iz - 1]) * (gamma_m1 * tempm[iz - 1]) ** 1.5)) ** (2.0 / 3.0)
+        else:
+            dl = 0.0
+        dtemp = gamma * polyad * gravz * dl
+        dlnrho = gamma * polyad * gravz * (1.0 - dl) / tempm[iz - 1]
+        tempm[iz] = tempm[iz - 1] - dtemp * dz
+        lnrhom[iz] = lnrhom[iz - 1] - dlnrho * dz
+    return lnrhom, tempm, math.exp(_interp1_descending(zz, lnrhom, z1))
+
+
+def mixinglength_stratification(flux, *, nzgrid, z0, Lz, z1, z2, gravz, gamma, cs20, mpoly0, mpoly1, rho0=1.0, cp=1.0):
+    """mixinglength (entropy.f90:2108-2218): secant iteration on rho at the top until rho(z1) = rho0, then rho0 := rhotop
+    (the value run.x reads back from param.nml, written after the initial condition, start.f90:562).
+    -> lnrho(z), ss(z) bottom to top, the new lnrho0"""
+    kw = dict(nzgrid=nzgrid, ztop=z0 + Lz, dz=Lz / (nzgrid - 1), z1=z1, z2=z2, gravz=gravz, gamma=gamma, cs2top=cs20,
+              mpoly0=mpoly0, mpoly1=mpoly1)
+    rbot, rt_old, rt_new = rho0, 0.1 * rho0, 0.12 * rho0
+    rb_old = strat_MLT(rt_old, flux, **kw)[2]
+    lnrhom, tempm, rb_new = strat_MLT(rt_new, flux, **kw)
+    for _ in range(10):
+        rhotop = rt_old + (rt_new - rt_old) / (rb_new - rb_old) * (rbot - rb_old)
+        if abs(rhotop / rt_new - 1.0) <= 1e-4:
+            break
+        lnrhom, tempm, rhobot = strat_MLT(rhotop, flux, **kw)
+        rt_old, rb_old, rt_new, rb_new = rt_new, rb_new, rhotop, rhobot
+    lnrho0 = math.log(rhotop)
+    gamma_m1, cv = gamma - 1.0, cp / gamma
+    lnTT0 = math.log(cs20 / (cp * gamma_m1))
+    lnrho = lnrhom[::-1].copy()                                    # f(n) = lnrhom(nzgrid-iz+1)
+    ss = cv * (np.log(tempm[::-1]) - lnTT0 - gamma_m1 * (lnrho - lnrho0))       # eoscalc(ilnrho_lnTT), eos_idealgas.f90
+    return lnrho, ss, lnrho0
