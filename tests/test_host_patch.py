@@ -148,3 +148,49 @@ def test_fortran_mirrors_of_the_abi_structs_match_the_header():
         assert len(c) == len(fm) and len(c) > 3, (name, len(c), len(fm))
         for a, b in zip(c, fm):
             assert a == b, (name, a, b)
+
+
+def test_wrapper_block_structure_is_balanced():
+    """no Fortran compiler in this image: at least every block of gpu_b200.f90 that opens closes with its own keyword, in
+    order (module/type/interface/subroutine/function/if-then/do/select/where), continuation lines joined"""
+    import re
+    src = open(os.path.join(ROOT, "pencil-code_b200", "fortran", "gpu_b200.f90")).read()
+    lines, cur = [], ""
+    for ln in src.splitlines():
+        ln = re.sub(r"'[^']*'", "''", ln)
+        ln = ln.split("!")[0].rstrip()
+        if not ln.strip():
+            continue
+        if ln.rstrip().endswith("&"):
+            cur += ln.rstrip()[:-1] + " "
+            continue
+        lines.append((cur + ln).strip().lower())
+        cur = ""
+    stack = []
+    for full in lines:
+        for ln in (s.strip() for s in full.split(";")):            # `do ...; ...; enddo` on one line
+            if not ln:
+                continue
+            m = re.match(r"end\s*(module|type|interface|subroutine|function|if|do|select|where)\b", ln)
+            if m:
+                assert stack and stack[-1] == m.group(1), (ln, stack[-3:])
+                stack.pop()
+            elif re.match(r"module\s+\w+$", ln):
+                stack.append("module")
+            elif re.match(r"type\s*(,\s*bind\(c\))?\s*::", ln):
+                stack.append("type")
+            elif ln == "interface":
+                stack.append("interface")
+            elif re.match(r"(\w+\s+)*subroutine\s+\w+", ln):
+                stack.append("subroutine")
+            elif re.match(r"([\w()=]+\s+)*function\s+\w+\s*\(", ln):
+                stack.append("function")
+            elif re.match(r"(\w+\s*:\s*)?if\s*\(.*\)\s*then$", ln):
+                stack.append("if")
+            elif re.match(r"(\w+\s*:\s*)?do(\s+\w+\s*=.*)?$", ln):
+                stack.append("do")
+            elif re.match(r"select\s+case", ln):
+                stack.append("select")
+            elif re.match(r"where\s*\([^)]*\)$", ln):
+                stack.append("where")
+    assert stack == [], stack
