@@ -194,3 +194,40 @@ def test_wrapper_block_structure_is_balanced():
             elif re.match(r"where\s*\([^)]*\)$", ln):
                 stack.append("where")
     assert stack == [], stack
+
+
+def test_wrapper_interface_block_matches_the_c_prototypes():
+    """every bind(C) interface of gpu_b200.f90 against its prototype in include/pcb200.h: same number of arguments,
+    by-value vs by-reference, and int / double / char / struct per argument"""
+    import re
+    h = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "pcb200.h")).read(), flags=re.S)
+    protos = {}
+    for ret, name, args in re.findall(r"^\s*(const char \*|int|void)\s*(pcb200_\w+)\s*\(([^)]*)\)\s*;", h, re.M):
+        out = []
+        for a in [x.strip() for x in args.split(",") if x.strip() and x.strip() != "void"]:
+            byref = "*" in a or "[" in a
+            base = "char" if re.search(r"\bchar\b", a) else "double" if "double" in a else "float" if "float" in a else \
+                   "struct" if re.search(r"pcb200_\w+", a) else "int"
+            out.append((base, byref))
+        protos[name] = (ret.strip(), out)
+    f = open(os.path.join(ROOT, "pencil-code_b200", "fortran", "gpu_b200.f90")).read()
+    block = re.search(r"\n  interface\n(.*?)\n  endinterface", f, re.S).group(1)
+    block = re.sub(r"&\s*\n\s*&?", " ", block)
+    n = 0
+    for m in re.finditer(r"function\s+(\w+)\s*\(([^)]*)\)\s*bind\(C,name='(\w+)'\)[^\n]*\n(.*?)endfunction", block, re.S | re.I):
+        fname, fargs, cname, body = m.group(1), [a.strip() for a in m.group(2).split(",") if a.strip()], m.group(3), m.group(4)
+        assert fname == cname and cname in protos, cname
+        decl = {}
+        for ln in body.splitlines():
+            if "::" not in ln or ln.strip().startswith("import"):
+                continue
+            spec, names = ln.split("::")
+            spec = spec.lower()
+            base = "char" if "character" in spec else "double" if "c_double" in spec else "float" if "c_float" in spec else \
+                   "struct" if "type(pcb200" in spec else "int"
+            for nm in names.split(","):
+                decl[nm.strip()] = (base, "value" not in spec)
+        got = [decl[a] for a in fargs]
+        assert got == protos[cname][1], (cname, got, protos[cname][1])
+        n += 1
+    assert n >= 15
