@@ -90,3 +90,15 @@ def write_var(path, f, t, x, y, z, dx, dy, dz, dtype=np.float64, rec_max=FREC_MA
         _write_record(fh, np.ascontiguousarray(f, dtype=dt).tobytes(), rec_max)
         tail = np.concatenate([[t], x, y, z, [dx, dy, dz]]).astype(dt)
         _write_record(fh, tail.tobytes(), rec_max)
+
+
+def append_persist(path, records):
+    """append the persistent block to a snapshot file that ends after record 2 (what the host does after
+    pcb200_snapshot_wait): {id: payload bytes} in the given order, framed by the block id (io_dist.f90:351-405)"""
+    with open(path, "ab") as fh:
+        _write_record(fh, struct.pack("<i", ID_BLOCK_PERSISTENT))
+        for rid, payload in records.items():
+            _write_record(fh, struct.pack("<i", rid))
+            _write_record(fh, bytes(payload))
+        _write_record(fh, struct.pack("<i", ID_BLOCK_PERSISTENT))
+

@@ -83,3 +83,17 @@ def test_double_precision_reference_snapshot_with_persistent_block(pk, tmp_path)
     snap.write_var(out, v["f"], v["t"], v["x"], v["y"], v["z"], v["dx"], v["dy"], v["dz"], dtype=np.float64)
     ours, ref = open(out, "rb").read(), open(path, "rb").read()
     assert ref[:len(ours)] == ours and len(ref) - len(ours) == sum(len(r) + 8 for r in snap.read_records(path)[2:])
+
+
+def test_snapshot_with_persistent_block_is_rewritten_byte_for_byte(pk, tmp_path):
+    """samples/backwards-compatible/data/proc0/var.dat (single precision, persistent block with the random-number state
+    and the forcing records): records 1-2 by write_var, the block by append_persist -> the same bytes"""
+    snap = pk.snapshot
+    src = os.path.join(HERE, "golden", "backwards-compatible.var.dat")
+    v = snap.read_var(src, 10, 10, 10, 7, np.float32)
+    per = snap.read_persist(src)
+    assert list(per)[0] == snap.ID_RECORD_RANDOM_SEEDS and len(per) >= 3
+    out = str(tmp_path / "var.dat")
+    snap.write_var(out, v["f"], v["t"], v["x"], v["y"], v["z"], v["dx"], v["dy"], v["dz"], dtype=np.float32)
+    snap.append_persist(out, per)
+    assert open(out, "rb").read() == open(src, "rb").read()
