@@ -231,3 +231,44 @@ def test_wrapper_interface_block_matches_the_c_prototypes():
         assert got == protos[cname][1], (cname, got, protos[cname][1])
         n += 1
     assert n >= 15
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")), reason="reference tree not here")
+def test_every_free_identifier_of_the_wrapper_exists_in_the_host():
+    """names gpu_b200.f90 takes from whole-module imports (Cdata incl. Cparam and the generated cparam.inc switches,
+    Particles_cdata): each must be declared in cdata.f90 / cparam.f90 / particles_cdata.f90 or be a module switch that
+    some src/*.f90 header announces with `! CPARAM logical, parameter :: l... =`"""
+    import glob
+    import re
+    src = open(os.path.join(ROOT, "pencil-code_b200", "fortran", "gpu_b200.f90")).read()
+    code = re.sub(r"!.*", "", src)
+    code = re.sub(r"'[^']*'", "''", code)
+    code = re.sub(r"&\s*\n\s*&?", " ", code)
+    low = code.lower()
+    ids = set(re.findall(r"[a-z_]\w*", low))
+    declared = set()
+    for m in re.finditer(r"::\s*([^\n]*)", low):                              # local declarations and struct members
+        declared.update(re.findall(r"[a-z_]\w*", m.group(1)))
+    for m in re.finditer(r"(?<![a-z])(?:subroutine|function|module|type(?:,\s*bind\(c\))?\s*::)[ \t]+(\w+)", low):
+        declared.add(m.group(1))
+    for m in re.finditer(r"(?:subroutine|function)\s+\w+\s*\(([^)]*)\)", low):
+        declared.update(a.strip() for a in m.group(1).split(","))
+    for m in re.finditer(r"use\s+(\w+)\s*,\s*only\s*:\s*([^\n]*)", low):      # explicit imports (checked by the test above)
+        declared.add(m.group(1))
+        declared.update(re.findall(r"[a-z_]\w*", m.group(2)))
+    declared.update(m.group(1) for m in re.finditer(r"use\s*(?:,\s*intrinsic\s*::)?\s*(\w+)", low))
+    host = ""
+    for f in ("src/cdata.f90", "src/cparam.f90", "src/particles_cdata.f90", "samples/conv-slab/src/cparam.local"):   # cparam.f90 includes cparam.local
+        host += open(os.path.join(REF, f), errors="replace").read().lower()
+    host_ids = set(re.findall(r"[a-z_]\w*", host))
+    switches = set()
+    for f in glob.glob(os.path.join(REF, "src", "*.f90")):
+        head = open(f, errors="replace").read(6000).lower()
+        switches.update(re.findall(r"!\s*cparam\s+logical\s*,\s*parameter\s*::\s*(l\w+)", head))
+    keywords = set("""use only intrinsic implicit none include integer parameter type bind c endtype real logical character len
+        kind dimension save pointer null contains subroutine endsubroutine function endfunction result import value intent in out
+        inout interface endinterface if then else endif do enddo exit call return select case default endselect trim merge int all
+        mod exp transfer associated nullify where elsewhere endwhere target contiguous module endmodule and or not true false name
+        c_int c_int32_t c_double c_char c_ptr c_null_char c_null_ptr c_f_pointer _c_int""".split())
+    free = sorted(i for i in ids if i not in declared and i not in keywords and i not in host_ids and i not in switches)
+    assert free == [], free
