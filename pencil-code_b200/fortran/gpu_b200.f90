@@ -385,7 +385,9 @@ contains
         prof=exp(-0.5*((xyz0(3)+Lxyz(3)-z(n1:n2))/wcool)**2)
         call check(pcb200_set_zprofile(2_c_int,prof,int(nz,c_int)),'initialize_GPU')
       endif
-      if (lparticles) call initialize_particles_GPU
+!  particles: their parameters are complete only after particles_initialize_modules, which run.f90 calls AFTER
+!  initialize_modules (run.f90:408,429; RELOAD :571-572: rhop_swarm, mp_swarm are computed there), so
+!  pcb200_particles_initialize waits for the first rhs_GPU (lvery_first)
       lvery_first=.true.      ! force a full upload after RELOAD / rsnap
 !
     endsubroutine initialize_GPU
@@ -468,7 +470,10 @@ contains
 !
 !  particles travel with f: uploaded once, then owned by the device
 !  (the host skips particles_timestep_first/second and particles_boundconds when lgpu)
-      if (lparticles .and. lvery_first) call check(pcb200_particles_load(fp,ipar),'rhs_GPU')
+      if (lparticles .and. lvery_first) then
+        call initialize_particles_GPU
+        call check(pcb200_particles_load(fp,ipar),'rhs_GPU')
+      endif
       dtc=dt
       call check(pcb200_substep(int(isubstep,c_int),merge(1_c_int,0_c_int,lvery_first), &
                                 merge(1_c_int,0_c_int,early_finalize),merge(1_c_int,0_c_int,ldiagnos),dtc),'rhs_GPU')
