@@ -322,8 +322,8 @@ contains
       if (lgravz .and. gravz_profile/='const') str=trim(str)//', '//'gravz_profile/=const'
       if (lgravx .or. lgravy) str=trim(str)//', '//'gravity along x or y'
 !  Not visible from here (module-private, not handed out by pushpars2c): ivisc, iresistivity, lweyl_gauge,
-!  hydro's theta.  The device implements ivisc='nu-const', iresistivity='eta-const', the Weyl gauge and
-!  theta=0 (the defaults of the samples this path covers); INTEGRATION.md lists them.
+!  hydro's theta, forcing's iforce.  The device implements ivisc='nu-const', iresistivity='eta-const', the Weyl
+!  gauge, theta=0 and iforce='helical' (the settings of the samples this path covers); INTEGRATION.md lists them.
       if (str/='') call fatal_error('initialize_GPU','No GPU implementation for "'//trim(str(3:))//'"')
 !
       par%abi_version=PCB200_ABI_VERSION
